@@ -1,0 +1,162 @@
+/* rt_b200.h — C-ABI of the B200-native path-tracing core (librt_b200.so).
+ *
+ * The reference (daRoyalCacti/Raytracing_GPU) has no library boundary: its de-facto operator interface is
+ *     void draw(scene& curr_scene, render_settings settings)            render.h:118
+ * fed by the device-side constructors that scenes.h calls.  Each entry point below names the
+ * reference interface it replaces.  Plain pointers and sizes only; no torch / C++ types.
+ *
+ * Conventions: every function returns >= 0 on success (a resource index where one is created) and a
+ * negative rt_status on failure; rt_last_error() returns the message of the calling thread's last failure.
+ * The library never calls exit() (the reference's checkCudaErrors does: common.h:30-38).
+ * A scene is not thread-safe; distinct scenes may be used from distinct threads.
+ * Scene recording, flattening and export are host-only and work without a GPU; rt_scene_commit,
+ * rt_first_hit and rt_render* need a CUDA device and fail with RT_ERR_CUDA when there is none —
+ * there is no CPU fallback.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "rt_flat.h"
+#include "rt_program.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rt_scene rt_scene;
+
+enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1,    /* bad argument / index / malformed program */
+    RT_ERR_STATE = -2,      /* call order (e.g. render before commit) */
+    RT_ERR_CUDA = -3,       /* CUDA runtime error or no device */
+    RT_ERR_UNSUPPORTED = -4 /* graph shape outside what the flattener supports */
+};
+
+const char* rt_last_error(void);
+const char* rt_version(void);
+
+/* ---- scene lifetime: replaces struct scene's ctor/dtor (scenes.h:36-67) ---- */
+int rt_scene_create(rt_scene** out);
+void rt_scene_destroy(rt_scene* s);
+
+/* ---- textures (texture.h:12-164) ---- */
+int rt_tex_solid(rt_scene* s, float r, float g, float b);                           /* solid_color            texture.h:14 */
+int rt_tex_checker(rt_scene* s, int even_tex, int odd_tex);                         /* checker_texture        texture.h:31 */
+int rt_perlin_tables(rt_scene* s, const float* ranvec768, const int32_t* perm768);  /* perlin(curandState*)   perlin.h:63 (tables made by the caller) */
+int rt_tex_noise(rt_scene* s, int perlin, float scale);                             /* noise_texture          texture.h:53 */
+int rt_tex_turbulent(rt_scene* s, int perlin, float scale, int depth);              /* turbulent_texture      texture.h:70 */
+int rt_tex_marble(rt_scene* s, int perlin, float scale);                            /* marble_texture         texture.h:84 */
+int rt_image(rt_scene* s, const uint8_t* pixels, int width, int height, int bytes_per_pixel); /* make_image texture.h:188 (decoded bytes; copied) */
+int rt_tex_image(rt_scene* s, int image);                                           /* image_texture          texture.h:125 */
+
+/* ---- materials (material.h) ---- */
+int rt_mat_lambertian(rt_scene* s, int tex);            /* material.h:19-22 */
+int rt_mat_metal(rt_scene* s, int tex, float fuzz);     /* material.h:45-48 */
+int rt_mat_dielectric(rt_scene* s, float ir);           /* material.h:62 */
+int rt_mat_diffuse_light(rt_scene* s, int tex);         /* material.h:110-113 */
+int rt_mat_isotropic(rt_scene* s, int tex);             /* material.h:128-131 */
+
+/* ---- hittables ---- */
+int rt_sphere(rt_scene* s, float cx, float cy, float cz, float radius, int mat);                         /* sphere.h:13 */
+int rt_moving_sphere(rt_scene* s, const float c0[3], const float c1[3], float t0, float t1, float radius, int mat); /* moving_sphere.h:13 */
+int rt_xy_rect(rt_scene* s, float x0, float x1, float y0, float y1, float k, int mat);                   /* aarect.h:13 */
+int rt_xz_rect(rt_scene* s, float x0, float x1, float z0, float z1, float k, int mat);                   /* aarect.h:32 */
+int rt_yz_rect(rt_scene* s, float y0, float y1, float z0, float z1, float k, int mat);                   /* aarect.h:50 */
+int rt_box(rt_scene* s, const float p0[3], const float p1[3], int mat);                                  /* box.h:14 */
+int rt_triangle(rt_scene* s, const float v[9], const float uv[6], const float* normals9_or_null, int mat); /* triangle.h:19, :34 */
+/* One mesh object as create_meshes_d builds it (triangle_mesh.h:147-204, single object): triangle k uses
+ * vertices/normals/uvs of indices[3k..3k+2]; returns the triangle_mesh hittable (triangle_mesh.h:26). */
+int rt_mesh(rt_scene* s, const float* vertices, int n_vertices, const uint32_t* indices, int n_triangles,
+            const float* uvs, const float* normals, int mat);
+int rt_translate(rt_scene* s, int child, float dx, float dy, float dz);       /* hittable.h:35 */
+int rt_rotate_y(rt_scene* s, int child, float angle_degrees);                  /* hittable.h:78 */
+int rt_rotate_y_sincos(rt_scene* s, int child, float sin_theta, float cos_theta);
+int rt_constant_medium(rt_scene* s, int boundary, float density, int tex);     /* constant_medium.h:15 */
+int rt_constant_medium_nid(rt_scene* s, int boundary, float neg_inv_density, int tex);
+int rt_list(rt_scene* s, const int* children, int n);                          /* hittable_list.h:12 */
+int rt_bvh(rt_scene* s, const int* children, int n);                           /* bvh.h:136 — grouping hint: everything lands in the one LBVH */
+
+/* ---- world / camera / background ---- */
+int rt_set_world(rt_scene* s, int hittable);                                   /* *d_world = ...            scenes.h:88 etc. */
+int rt_set_background(rt_scene* s, float r, float g, float b);                 /* scene::set_background     scenes.h:69 */
+int rt_set_camera(rt_scene* s, const float lookfrom[3], const float lookat[3], const float vup[3], float vfov_degrees,
+                  float aspect_ratio, float aperture, float focus_dist, float time0, float time1); /* camera.h:18 */
+int rt_set_camera_raw(rt_scene* s, const rt_flat_camera* cam);
+
+/* ---- bulk: replay a scene program (include/rt_program.h) through the calls above ---- */
+int rt_scene_replay(rt_scene* s, const uint32_t* words, size_t n_words);
+
+/* ---- flatten + export (host only) ---- */
+int rt_scene_flatten(rt_scene* s);                          /* returns the number of leaf ids */
+size_t rt_scene_export_size(rt_scene* s);                   /* 0 if not flattened */
+int rt_scene_export(rt_scene* s, void* buf, size_t cap);    /* layout: rt_flat.h */
+
+/* image_height = int(width / aspect) in double, as render_settings::calc_height (render.h:32) */
+int rt_image_height(int width, float aspect);
+
+/* ---- device side ---- */
+typedef struct rt_build_stats {
+    uint32_t n_prims, n_nodes;
+    float ms_upload, ms_morton, ms_sort, ms_hierarchy, ms_refit, ms_collapse, ms_total;
+} rt_build_stats;
+
+/* Flatten (if needed), upload to `device` and build the LBVH there.  Replaces the one-thread device
+ * constructors create_*_world<<<1,1>>> + bvh_node::bvh_node (scenes.h:82..., bvh.h:270-346). */
+int rt_scene_commit(rt_scene* s, int device, rt_build_stats* stats_or_null);
+
+/* Closest hit for a caller-supplied ray set — what color_f asks of the world at render.h:63.
+ * rays: n x 7 floats (origin, direction, time), host memory.  xi: NULL, or n floats in (0,1]: the value used
+ * for every constant_medium free-flight draw of that ray (constant_medium.h:57); with NULL media are skipped.
+ * prim_id: DFS leaf id or -1; t: hit distance (+inf on miss). */
+int rt_first_hit(rt_scene* s, const float* rays, int n, float t_min, const float* xi, int32_t* prim_id, float* t);
+
+enum rt_render_flags {
+    RT_RENDER_DEFAULT = 0,
+    RT_RENDER_COUNTERS = 1  /* fill the traversal counters in rt_render_stats (slower) */
+};
+
+typedef struct rt_render_settings {  /* replaces render_settings (render.h:21-50) */
+    uint32_t width, height;
+    uint32_t samples_per_pixel;      /* total over all ranks: samples_per_pixel_per_fb * no_fb */
+    uint32_t max_depth;              /* render.h:27, default 50 */
+    uint32_t seed;                   /* Philox key; the reference hard-codes 1984 (render.h:91) */
+    uint32_t sample_first;           /* this call renders sample indices [sample_first, sample_first+sample_count) */
+    uint32_t sample_count;           /* 0 = all */
+    uint32_t flags;
+    uint32_t pool_paths;             /* wavefront pool size in paths; 0 = default */
+    uint32_t reserved[7];
+} rt_render_settings;
+
+typedef struct rt_render_stats {
+    uint64_t samples;       /* camera paths started */
+    uint64_t rays;          /* path segments traced (closest-hit queries, render.h:63) */
+    uint64_t iterations;    /* wavefront iterations */
+    uint64_t kernel_launches;
+    float ms_total;         /* CUDA events, first ray-gen launch -> accumulation complete */
+    float ms_generate, ms_extend, ms_shade, ms_finish;
+    uint64_t nodes_visited, prim_tests; /* only with RT_RENDER_COUNTERS */
+    uint64_t reserved[4];
+} rt_render_stats;
+
+/* Render into host memory: out_rgb = width*height*3 floats, linear radiance, mean over the samples rendered
+ * by this call, row 0 = bottom of the image (render.h:105-112, color.h:23).  Replaces draw() minus file output. */
+int rt_render(rt_scene* s, const rt_render_settings* settings, float* out_rgb, rt_render_stats* stats_or_null);
+
+/* Same, but accumulates SUMS (not means) into a caller-owned device buffer of width*height*3 floats on the
+ * scene's device, on `cuda_stream` (a cudaStream_t cast to void*, NULL = default stream).  The buffer is added
+ * to, not cleared.  Multi-GPU: each rank renders its sample range, then the caller sums the buffers (one NCCL
+ * reduce) and divides by samples_per_pixel. */
+int rt_render_device(rt_scene* s, const rt_render_settings* settings, float* d_accum_rgb, void* cuda_stream,
+                     rt_render_stats* stats_or_null);
+
+/* Reference-exact 8-bit output stage (color.h:19-49): gamma-2, clamp to 0.999, *256, row flip. Host only.
+ * in: linear means, row 0 = bottom; out: width*height*3 bytes, row 0 = top. */
+int rt_quantize_frame(const float* rgb_linear, int width, int height, uint8_t* out_rgb8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

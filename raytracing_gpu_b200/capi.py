@@ -1,0 +1,237 @@
+"""ctypes binding of include/rt_b200.h.  Mirrors the C-ABI one to one (same names minus the ``rt_`` prefix)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def lib_path():
+    return os.path.join(_HERE, "librt_b200.so")
+
+
+class RtError(RuntimeError):
+    pass
+
+
+class RenderSettings(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("samples_per_pixel", C.c_uint32),
+                ("max_depth", C.c_uint32), ("seed", C.c_uint32), ("sample_first", C.c_uint32),
+                ("sample_count", C.c_uint32), ("flags", C.c_uint32), ("pool_paths", C.c_uint32),
+                ("reserved", C.c_uint32 * 7)]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("rays", C.c_uint64), ("iterations", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("ms_total", C.c_float), ("ms_generate", C.c_float),
+                ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_finish", C.c_float),
+                ("nodes_visited", C.c_uint64), ("prim_tests", C.c_uint64), ("reserved", C.c_uint64 * 4)]
+
+
+class BuildStats(C.Structure):
+    _fields_ = [("n_prims", C.c_uint32), ("n_nodes", C.c_uint32), ("ms_upload", C.c_float), ("ms_morton", C.c_float),
+                ("ms_sort", C.c_float), ("ms_hierarchy", C.c_float), ("ms_refit", C.c_float),
+                ("ms_collapse", C.c_float), ("ms_total", C.c_float)]
+
+
+RENDER_COUNTERS = 1
+
+_lib = None
+
+
+def lib():
+    """Load librt_b200.so.  Fails loudly when it has not been built (python __graft_entry__.py build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise RtError(f"{path} is missing: build it with `make -C raytracing_gpu_b200/csrc` "
+                      "(there is no CPU fallback)")
+    L = C.CDLL(path)
+    vp, i32, f32, u32p = C.c_void_p, C.c_int, C.c_float, C.POINTER(C.c_uint32)
+    sig = {
+        "rt_last_error": (C.c_char_p, []), "rt_version": (C.c_char_p, []),
+        "rt_scene_create": (i32, [C.POINTER(vp)]), "rt_scene_destroy": (None, [vp]),
+        "rt_tex_solid": (i32, [vp, f32, f32, f32]), "rt_tex_checker": (i32, [vp, i32, i32]),
+        "rt_perlin_tables": (i32, [vp, vp, vp]), "rt_tex_noise": (i32, [vp, i32, f32]),
+        "rt_tex_turbulent": (i32, [vp, i32, f32, i32]), "rt_tex_marble": (i32, [vp, i32, f32]),
+        "rt_image": (i32, [vp, vp, i32, i32, i32]), "rt_tex_image": (i32, [vp, i32]),
+        "rt_mat_lambertian": (i32, [vp, i32]), "rt_mat_metal": (i32, [vp, i32, f32]),
+        "rt_mat_dielectric": (i32, [vp, f32]), "rt_mat_diffuse_light": (i32, [vp, i32]),
+        "rt_mat_isotropic": (i32, [vp, i32]),
+        "rt_sphere": (i32, [vp, f32, f32, f32, f32, i32]),
+        "rt_moving_sphere": (i32, [vp, vp, vp, f32, f32, f32, i32]),
+        "rt_xy_rect": (i32, [vp, f32, f32, f32, f32, f32, i32]), "rt_xz_rect": (i32, [vp, f32, f32, f32, f32, f32, i32]),
+        "rt_yz_rect": (i32, [vp, f32, f32, f32, f32, f32, i32]), "rt_box": (i32, [vp, vp, vp, i32]),
+        "rt_triangle": (i32, [vp, vp, vp, vp, i32]), "rt_mesh": (i32, [vp, vp, i32, vp, i32, vp, vp, i32]),
+        "rt_translate": (i32, [vp, i32, f32, f32, f32]), "rt_rotate_y": (i32, [vp, i32, f32]),
+        "rt_rotate_y_sincos": (i32, [vp, i32, f32, f32]), "rt_constant_medium": (i32, [vp, i32, f32, i32]),
+        "rt_constant_medium_nid": (i32, [vp, i32, f32, i32]), "rt_list": (i32, [vp, vp, i32]),
+        "rt_bvh": (i32, [vp, vp, i32]), "rt_set_world": (i32, [vp, i32]),
+        "rt_set_background": (i32, [vp, f32, f32, f32]),
+        "rt_set_camera": (i32, [vp, vp, vp, vp, f32, f32, f32, f32, f32, f32]), "rt_set_camera_raw": (i32, [vp, vp]),
+        "rt_scene_replay": (i32, [vp, vp, C.c_size_t]), "rt_scene_flatten": (i32, [vp]),
+        "rt_scene_export_size": (C.c_size_t, [vp]), "rt_scene_export": (i32, [vp, vp, C.c_size_t]),
+        "rt_image_height": (i32, [i32, f32]), "rt_scene_commit": (i32, [vp, i32, C.POINTER(BuildStats)]),
+        "rt_first_hit": (i32, [vp, vp, i32, f32, vp, vp, vp]),
+        "rt_render": (i32, [vp, C.POINTER(RenderSettings), vp, C.POINTER(RenderStats)]),
+        "rt_render_device": (i32, [vp, C.POINTER(RenderSettings), vp, vp, C.POINTER(RenderStats)]),
+        "rt_quantize_frame": (i32, [vp, i32, i32, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)      # AttributeError here means the .so does not export a declared symbol
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+EXPORTED_SYMBOLS = None  # filled lazily by tests from include/rt_b200.h
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def image_height(width, aspect):
+    return lib().rt_image_height(int(width), float(aspect))
+
+
+def quantize_frame(rgb):
+    rgb = _f32(rgb)
+    h, w, _ = rgb.shape
+    out = np.empty((h, w, 3), np.uint8)
+    _check(lib().rt_quantize_frame(rgb.ctypes.data, w, h, out.ctypes.data))
+    return out
+
+
+def _check(rc):
+    if rc < 0:
+        raise RtError(f"rt_b200 error {rc}: {lib().rt_last_error().decode()}")
+    return rc
+
+
+class Scene:
+    """One rt_scene handle.  Method names and argument order follow include/rt_b200.h."""
+
+    def __init__(self):
+        self._h = C.c_void_p()
+        _check(lib().rt_scene_create(C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().rt_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __getattr__(self, name):
+        # scalar-argument constructors forward generically: scene.sphere(cx, cy, cz, r, mat) etc.
+        fn = getattr(lib(), "rt_" + name, None)
+        if fn is None:
+            raise AttributeError(name)
+
+        def call(*args):
+            for a in args:
+                if isinstance(a, (list, tuple, np.ndarray)):
+                    raise TypeError(f"rt_{name}: array argument needs the explicit wrapper")
+            return _check(fn(self._h, *args))
+        return call
+
+    # ---- constructors with array arguments ------------------------------------------------------
+    def moving_sphere(self, c0, c1, t0, t1, radius, mat):
+        a, b = _f32(c0), _f32(c1)
+        return _check(lib().rt_moving_sphere(self._h, a.ctypes.data, b.ctypes.data, t0, t1, radius, mat))
+
+    def box(self, p0, p1, mat):
+        a, b = _f32(p0), _f32(p1)
+        return _check(lib().rt_box(self._h, a.ctypes.data, b.ctypes.data, mat))
+
+    def triangle(self, v, uv, normals, mat):
+        a, b = _f32(v).reshape(9), _f32(uv).reshape(6)
+        n = _f32(normals).reshape(9) if normals is not None else None
+        return _check(lib().rt_triangle(self._h, a.ctypes.data, b.ctypes.data, n.ctypes.data if n is not None else None, mat))
+
+    def mesh(self, vertices, n_vertices, indices, n_triangles, uvs, normals, mat):
+        v, u, n = _f32(vertices), _f32(uvs), _f32(normals)
+        ix = np.ascontiguousarray(indices, dtype=np.uint32)
+        return _check(lib().rt_mesh(self._h, v.ctypes.data, int(n_vertices), ix.ctypes.data, int(n_triangles), u.ctypes.data,
+                                    n.ctypes.data, mat))
+
+    def image(self, pixels, width, height, bytes_per_pixel):
+        px = np.ascontiguousarray(pixels, dtype=np.uint8)
+        assert px.size == width * height * bytes_per_pixel
+        return _check(lib().rt_image(self._h, px.ctypes.data, width, height, bytes_per_pixel))
+
+    def perlin_tables(self, ranvec, perm):
+        r = _f32(ranvec).reshape(768)
+        p = np.ascontiguousarray(perm, dtype=np.int32).reshape(768)
+        return _check(lib().rt_perlin_tables(self._h, r.ctypes.data, p.ctypes.data))
+
+    def list(self, children, n=None):
+        c = np.ascontiguousarray(children, dtype=np.int32)
+        return _check(lib().rt_list(self._h, c.ctypes.data, c.size if n is None else n))
+
+    def bvh(self, children, n=None):
+        c = np.ascontiguousarray(children, dtype=np.int32)
+        return _check(lib().rt_bvh(self._h, c.ctypes.data, c.size if n is None else n))
+
+    def set_camera(self, lookfrom, lookat, vup, vfov, aspect, aperture, focus_dist, t0, t1):
+        a, b, c = _f32(lookfrom), _f32(lookat), _f32(vup)
+        return _check(lib().rt_set_camera(self._h, a.ctypes.data, b.ctypes.data, c.ctypes.data, vfov, aspect, aperture, focus_dist, t0, t1))
+
+    def set_camera_raw(self, cam24):
+        c = _f32(cam24).reshape(24)
+        return _check(lib().rt_set_camera_raw(self._h, c.ctypes.data))
+
+    # ---- helpers with array arguments -----------------------------------------------------------
+    def replay(self, program):
+        program = np.ascontiguousarray(program, dtype=np.uint32)
+        return _check(lib().rt_scene_replay(self._h, program.ctypes.data, program.size))
+
+    def flatten(self):
+        return _check(lib().rt_scene_flatten(self._h))
+
+    def export(self):
+        self.flatten()
+        n = lib().rt_scene_export_size(self._h)
+        buf = np.zeros(n, np.uint8)
+        _check(lib().rt_scene_export(self._h, buf.ctypes.data, n))
+        return buf
+
+    def commit(self, device=0):
+        st = BuildStats()
+        _check(lib().rt_scene_commit(self._h, int(device), C.byref(st)))
+        return st
+
+    def first_hit(self, rays, t_min=0.001, xi=None):
+        rays = _f32(rays).reshape(-1, 7)
+        n = rays.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        xi_a = _f32(xi) if xi is not None else None
+        _check(lib().rt_first_hit(self._h, rays.ctypes.data, n, float(t_min), xi_a.ctypes.data if xi_a is not None else None,
+                                  ids.ctypes.data, t.ctypes.data))
+        return ids, t
+
+    def render(self, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0, flags=0, pool_paths=0):
+        st = RenderSettings(width=width, height=height, samples_per_pixel=spp, max_depth=max_depth, seed=seed,
+                            sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths)
+        out = np.empty((height, width, 3), np.float32)
+        stats = RenderStats()
+        _check(lib().rt_render(self._h, C.byref(st), out.ctypes.data, C.byref(stats)))
+        return out, stats
+
+    def render_device(self, d_accum_ptr, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0,
+                      flags=0, pool_paths=0, stream=None):
+        """Accumulate sums into a caller-owned device buffer (e.g. a torch CUDA tensor's data_ptr())."""
+        st = RenderSettings(width=width, height=height, samples_per_pixel=spp, max_depth=max_depth, seed=seed,
+                            sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths)
+        stats = RenderStats()
+        _check(lib().rt_render_device(self._h, C.byref(st), C.c_void_p(d_accum_ptr), C.c_void_p(stream or 0), C.byref(stats)))
+        return stats

@@ -1,0 +1,426 @@
+// bvh_build.cu — GPU LBVH construction (replaces the reference's one-thread bvh_node build, bvh.h:163-346).
+//
+// Pipeline, all on the device, no CUB/thrust:
+//   prim_bounds   world AABB per primitive (local box pushed through its translate/rotate_y chain) + centroid
+//                 bounds of the scene (warp/block reduce, ordered-int atomics)
+//   morton        63-bit Morton code of the centroid (21 bits per axis)
+//   radix sort    LSD, 8 bits per pass, (u64 key, u32 value), 3 kernels per pass: per-tile histogram,
+//                 single-block exclusive scan of the digit-major table, stable scatter (warp match ranking);
+//                 passes whose digit is constant over all keys are skipped
+//   karras        internal nodes from sorted codes (Karras 2012), duplicates split by index
+//   refit         bottom-up boxes, one atomic counter per internal node
+//   emit          64-byte traversal nodes (parent holds both child boxes) + primitives permuted into leaf order
+#include "device_scene.cuh"
+
+#include <cfloat>
+#include <vector>
+
+namespace rtb {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------
+// bounds
+// ---------------------------------------------------------------------------------------------------
+struct Box { float3 lo, hi; };
+
+__device__ __forceinline__ void grow(Box& b, float x, float y, float z) {
+    b.lo.x = fminf(b.lo.x, x); b.lo.y = fminf(b.lo.y, y); b.lo.z = fminf(b.lo.z, z);
+    b.hi.x = fmaxf(b.hi.x, x); b.hi.y = fmaxf(b.hi.y, y); b.hi.z = fmaxf(b.hi.z, z);
+}
+
+__device__ __forceinline__ Box empty_box() {
+    Box b; b.lo = make_float3(FLT_MAX, FLT_MAX, FLT_MAX); b.hi = make_float3(-FLT_MAX, -FLT_MAX, -FLT_MAX); return b;
+}
+
+// object-space box of a primitive over the shutter interval [t_lo, t_hi]
+__device__ Box local_box(const DPrim& p, float t_lo, float t_hi) {
+    Box b = empty_box();
+    const uint32_t type = p.type_chain & 15u;
+    if (type == RT_PRIM_SPHERE) {
+        const float r = fabsf(p.a.w);
+        grow(b, p.a.x - r, p.a.y - r, p.a.z - r); grow(b, p.a.x + r, p.a.y + r, p.a.z + r);
+    } else if (type == RT_PRIM_MOVING_SPHERE) {
+        const float r = fabsf(p.c0);
+        const float ts[2] = {t_lo, t_hi};
+        for (int k = 0; k < 2; k++) {   // the centre moves linearly: the extremes are at the interval ends
+            const float w = (ts[k] - p.b.z) / (p.b.w - p.b.z);
+            const float cx = p.a.x + w * (p.a.w - p.a.x), cy = p.a.y + w * (p.b.x - p.a.y), cz = p.a.z + w * (p.b.y - p.a.z);
+            grow(b, cx - r, cy - r, cz - r); grow(b, cx + r, cy + r, cz + r);
+        }
+    } else if (type == RT_PRIM_TRIANGLE) {
+        grow(b, p.a.x, p.a.y, p.a.z);
+        grow(b, p.a.x + p.a.w, p.a.y + p.b.x, p.a.z + p.b.y);
+        grow(b, p.a.x + p.b.z, p.a.y + p.b.w, p.a.z + p.c0);
+    } else {
+        const float a0 = fminf(p.a.x, p.a.y), a1 = fmaxf(p.a.x, p.a.y), b0 = fminf(p.a.z, p.a.w), b1 = fmaxf(p.a.z, p.a.w), k = p.b.x;
+        if (type == RT_PRIM_XY_RECT) { grow(b, a0, b0, k); grow(b, a1, b1, k); }
+        else if (type == RT_PRIM_XZ_RECT) { grow(b, a0, k, b0); grow(b, a1, k, b1); }   // correct z extent (the reference's is degenerate)
+        else { grow(b, k, a0, b0); grow(b, k, a1, b1); }
+    }
+    return b;
+}
+
+// object space -> world: undo the chain from the innermost wrapper outwards
+__device__ Box world_box(const SceneView& sv, const DPrim& p, float t_lo, float t_hi) {
+    Box b = local_box(p, t_lo, t_hi);
+    const uint32_t chain = p.type_chain >> 4;
+    if (chain) {
+        const rt_flat_chain c = sv.chains[chain];
+        for (int k = (int)c.count - 1; k >= 0; k--) {
+            const rt_flat_xop op = sv.xops[c.first + k];
+            if (op.kind == RT_XOP_TRANSLATE) {
+                b.lo.x += op.a; b.lo.y += op.b; b.lo.z += op.c; b.hi.x += op.a; b.hi.y += op.b; b.hi.z += op.c;
+            } else {
+                Box r = empty_box();
+                for (int corner = 0; corner < 8; corner++) {
+                    const float x = (corner & 1) ? b.hi.x : b.lo.x, y = (corner & 2) ? b.hi.y : b.lo.y, z = (corner & 4) ? b.hi.z : b.lo.z;
+                    grow(r, op.b * x + op.a * z, y, -op.a * x + op.b * z);   // hittable.h:131-132
+                }
+                b = r;
+            }
+        }
+    }
+    // conservative padding: flat primitives get thickness, and every box absorbs the rounding of the
+    // transforms above (absolute + relative)
+    const float m = fmaxf(fmaxf(fmaxf(fabsf(b.lo.x), fabsf(b.hi.x)), fmaxf(fabsf(b.lo.y), fabsf(b.hi.y))), fmaxf(fabsf(b.lo.z), fabsf(b.hi.z)));
+    const float pad = 1e-4f + 4e-6f * m;
+    b.lo.x -= pad; b.lo.y -= pad; b.lo.z -= pad; b.hi.x += pad; b.hi.y += pad; b.hi.z += pad;
+    return b;
+}
+
+// order-preserving float <-> uint mapping for atomicMin / atomicMax
+__device__ __forceinline__ uint32_t f2ord(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__host__ __device__ __forceinline__ float ord2f(uint32_t o) {
+    const uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+
+__global__ void k_prim_bounds(SceneView sv, const DPrim* prims, uint32_t n, float t_lo, float t_hi,
+                              float4* box_lo, float4* box_hi, uint32_t* scene_ord /* [6]: min xyz, max xyz of centroids */) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float cx = FLT_MAX, cy = FLT_MAX, cz = FLT_MAX, dx = -FLT_MAX, dy = -FLT_MAX, dz = -FLT_MAX;
+    if (i < n) {
+        const Box b = world_box(sv, prims[i], t_lo, t_hi);
+        box_lo[i] = make_float4(b.lo.x, b.lo.y, b.lo.z, 0.f);
+        box_hi[i] = make_float4(b.hi.x, b.hi.y, b.hi.z, 0.f);
+        cx = dx = 0.5f * (b.lo.x + b.hi.x); cy = dy = 0.5f * (b.lo.y + b.hi.y); cz = dz = 0.5f * (b.lo.z + b.hi.z);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        cx = fminf(cx, __shfl_xor_sync(0xffffffffu, cx, o)); cy = fminf(cy, __shfl_xor_sync(0xffffffffu, cy, o));
+        cz = fminf(cz, __shfl_xor_sync(0xffffffffu, cz, o)); dx = fmaxf(dx, __shfl_xor_sync(0xffffffffu, dx, o));
+        dy = fmaxf(dy, __shfl_xor_sync(0xffffffffu, dy, o)); dz = fmaxf(dz, __shfl_xor_sync(0xffffffffu, dz, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(&scene_ord[0], f2ord(cx)); atomicMin(&scene_ord[1], f2ord(cy)); atomicMin(&scene_ord[2], f2ord(cz));
+        atomicMax(&scene_ord[3], f2ord(dx)); atomicMax(&scene_ord[4], f2ord(dy)); atomicMax(&scene_ord[5], f2ord(dz));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Morton codes
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t spread21(uint32_t v) {   // 21 bits -> every third bit of 63
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void k_morton(const float4* box_lo, const float4* box_hi, uint32_t n, const uint32_t* scene_ord, uint64_t* keys, uint32_t* vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float lx = ord2f(scene_ord[0]), ly = ord2f(scene_ord[1]), lz = ord2f(scene_ord[2]);
+    const float ex = fmaxf(ord2f(scene_ord[3]) - lx, 1e-30f), ey = fmaxf(ord2f(scene_ord[4]) - ly, 1e-30f), ez = fmaxf(ord2f(scene_ord[5]) - lz, 1e-30f);
+    const float4 lo = box_lo[i], hi = box_hi[i];
+    const float scale = 2097151.0f;   // 2^21 - 1
+    const uint32_t qx = (uint32_t)fminf(fmaxf((0.5f * (lo.x + hi.x) - lx) / ex * scale, 0.f), scale);
+    const uint32_t qy = (uint32_t)fminf(fmaxf((0.5f * (lo.y + hi.y) - ly) / ey * scale, 0.f), scale);
+    const uint32_t qz = (uint32_t)fminf(fmaxf((0.5f * (lo.z + hi.z) - lz) / ez * scale, 0.f), scale);
+    keys[i] = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
+    vals[i] = i;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// radix sort: (u64 key, u32 value), LSD 8 bits per pass
+// ---------------------------------------------------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ROUNDS = 8;                         // keys per thread
+constexpr int SORT_TILE = SORT_THREADS * SORT_ROUNDS;  // keys per block
+
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const uint64_t* keys, uint32_t n, int shift, uint32_t* counts /* [256][nblocks] */) {
+    __shared__ uint32_t hist[256];
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * SORT_TILE;
+    for (int r = 0; r < SORT_ROUNDS; r++) {
+        const uint32_t i = base + r * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&hist[(uint32_t)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    counts[threadIdx.x * gridDim.x + blockIdx.x] = hist[threadIdx.x];
+}
+
+// exclusive scan of `len` counters by one block; also reports whether one digit holds all n keys
+__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t* counts, uint32_t len, uint32_t nblocks, uint32_t n, uint32_t* pass_is_trivial) {
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry;
+    __shared__ uint32_t trivial;
+    if (threadIdx.x == 0) { carry = 0; trivial = 0; }
+    __syncthreads();
+    // trivial-pass detection: digit d is constant iff sum_b counts[d][b] == n
+    for (uint32_t d = threadIdx.x; d < 256; d += blockDim.x) {
+        uint32_t s = 0;
+        for (uint32_t b = 0; b < nblocks; b++) s += counts[d * nblocks + b];
+        if (s == n) trivial = 1;
+    }
+    __syncthreads();
+    for (uint32_t base = 0; base < len; base += blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < len ? counts[i] : 0;
+        uint32_t x = v;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((threadIdx.x & 31) >= o) x += y; }
+        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_sums[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, w, o); if (threadIdx.x >= o) w += y; }
+            warp_sums[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const uint32_t warp_prefix = (threadIdx.x >> 5) ? warp_sums[(threadIdx.x >> 5) - 1] : 0;
+        if (i < len) counts[i] = carry + warp_prefix + x - v;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry += warp_prefix + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *pass_is_trivial = trivial;
+}
+
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                                                               uint32_t n, int shift, const uint32_t* offsets /* scanned [256][nblocks] */,
+                                                               const uint32_t* pass_is_trivial) {
+    __shared__ uint32_t digit_base[256];                       // running global offset of this block per digit
+    __shared__ uint32_t warp_count[SORT_THREADS / 32][256];    // per round
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t base = blockIdx.x * SORT_TILE;
+    if (*pass_is_trivial) {   // constant digit: order is unchanged, plain copy keeps the ping-pong consistent
+        for (int r = 0; r < SORT_ROUNDS; r++) {
+            const uint32_t i = base + r * SORT_THREADS + threadIdx.x;
+            if (i < n) { keys_out[i] = keys_in[i]; vals_out[i] = vals_in[i]; }
+        }
+        return;
+    }
+    digit_base[threadIdx.x] = offsets[threadIdx.x * gridDim.x + blockIdx.x];
+    for (int r = 0; r < SORT_ROUNDS; r++) {
+        for (int w = 0; w < SORT_THREADS / 32; w++) warp_count[w][threadIdx.x] = 0;
+        __syncthreads();
+        const uint32_t i = base + r * SORT_THREADS + threadIdx.x;
+        const bool valid = i < n;
+        uint64_t key = 0; uint32_t val = 0; uint32_t digit = 256 + lane;   // invalid lanes never match anyone
+        if (valid) { key = keys_in[i]; val = vals_in[i]; digit = (uint32_t)(key >> shift) & 255u; }
+        const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        const uint32_t rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+        if (valid && rank_in_warp == 0) warp_count[warp][digit] = __popc(peers);
+        __syncthreads();
+        if (valid) {
+            uint32_t before = 0;
+            for (uint32_t w = 0; w < warp; w++) before += warp_count[w][digit];
+            const uint32_t dst = digit_base[digit] + before + rank_in_warp;
+            keys_out[dst] = key; vals_out[dst] = val;
+        }
+        __syncthreads();
+        uint32_t total = 0;
+        for (int w = 0; w < SORT_THREADS / 32; w++) total += warp_count[w][threadIdx.x];
+        digit_base[threadIdx.x] += total;
+        __syncthreads();
+    }
+}
+
+} // namespace
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------
+// Karras hierarchy over sorted keys
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int delta(const uint64_t* keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((uint32_t)i ^ (uint32_t)j);   // duplicates: fall back to the index
+    return __clzll((long long)(a ^ b));
+}
+
+// children encoding: >= 0 internal node index, < 0 leaf (~leaf index in sorted order)
+__global__ void k_karras(const uint64_t* keys, int n, int* left, int* right, int* parent_internal, int* parent_leaf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    if (lo == gamma) { left[i] = ~gamma; parent_leaf[gamma] = i; } else { left[i] = gamma; parent_internal[gamma] = i; }
+    if (hi == gamma + 1) { right[i] = ~(gamma + 1); parent_leaf[gamma + 1] = i; } else { right[i] = gamma + 1; parent_internal[gamma + 1] = i; }
+    if (i == 0) parent_internal[0] = -1;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// bottom-up refit
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_refit(int n, const uint32_t* sorted_vals, const float4* prim_lo, const float4* prim_hi, const int* left, const int* right,
+                        const int* parent_internal, const int* parent_leaf, float4* leaf_lo, float4* leaf_hi, float4* node_lo,
+                        float4* node_hi, uint32_t* visit) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t p = sorted_vals[j];
+    leaf_lo[j] = prim_lo[p];
+    leaf_hi[j] = prim_hi[p];
+    if (n == 1) return;
+    __threadfence();
+    int cur = parent_leaf[j];
+    while (cur >= 0) {
+        if (atomicAdd(&visit[cur], 1u) == 0) return;   // first arrival leaves; the second one owns the node
+        __threadfence();
+        const int l = left[cur], r = right[cur];
+        const volatile float4* llo = l < 0 ? &leaf_lo[~l] : &node_lo[l];
+        const volatile float4* lhi = l < 0 ? &leaf_hi[~l] : &node_hi[l];
+        const volatile float4* rlo = r < 0 ? &leaf_lo[~r] : &node_lo[r];
+        const volatile float4* rhi = r < 0 ? &leaf_hi[~r] : &node_hi[r];
+        node_lo[cur] = make_float4(fminf(llo->x, rlo->x), fminf(llo->y, rlo->y), fminf(llo->z, rlo->z), 0.f);
+        node_hi[cur] = make_float4(fmaxf(lhi->x, rhi->x), fmaxf(lhi->y, rhi->y), fmaxf(lhi->z, rhi->z), 0.f);
+        __threadfence();
+        cur = parent_internal[cur];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// traversal layout + primitive permutation
+// ---------------------------------------------------------------------------------------------------
+__global__ void k_emit_nodes(int n, const int* left, const int* right, const float4* leaf_lo, const float4* leaf_hi,
+                             const float4* node_lo, const float4* node_hi, BNode* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n == 1) {
+        if (i == 0) {   // a single primitive: root with one real child and one empty slot
+            BNode b;
+            b.n0 = make_float4(leaf_lo[0].x, leaf_hi[0].x, leaf_lo[0].y, leaf_hi[0].y);
+            b.n1 = make_float4(FLT_MAX, -FLT_MAX, FLT_MAX, -FLT_MAX);
+            b.n2 = make_float4(leaf_lo[0].z, leaf_hi[0].z, FLT_MAX, -FLT_MAX);
+            b.child0 = ~0; b.child1 = ~0; b.pad0 = b.pad1 = 0;
+            out[0] = b;
+        }
+        return;
+    }
+    if (i >= n - 1) return;
+    const int l = left[i], r = right[i];
+    const float4 llo = l < 0 ? leaf_lo[~l] : node_lo[l], lhi = l < 0 ? leaf_hi[~l] : node_hi[l];
+    const float4 rlo = r < 0 ? leaf_lo[~r] : node_lo[r], rhi = r < 0 ? leaf_hi[~r] : node_hi[r];
+    BNode b;
+    b.n0 = make_float4(llo.x, lhi.x, llo.y, lhi.y);
+    b.n1 = make_float4(rlo.x, rhi.x, rlo.y, rhi.y);
+    b.n2 = make_float4(llo.z, lhi.z, rlo.z, rhi.z);
+    b.child0 = l; b.child1 = r; b.pad0 = b.pad1 = 0;
+    out[i] = b;
+}
+
+__global__ void k_permute_prims(uint32_t n, const uint32_t* sorted_vals, const DPrim* in, const uint32_t* leaf_ids_in, DPrim* out, uint32_t* leaf_ids_out) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t p = sorted_vals[j];
+    out[j] = in[p];
+    leaf_ids_out[j] = leaf_ids_in[p];
+}
+
+template <class T> cudaError_t dalloc(T** p, size_t count) { return cudaMalloc((void**)p, (count ? count : 1) * sizeof(T)); }
+
+} // namespace
+
+int build_lbvh(DeviceScene& ds, const DPrim* d_prims_in, const uint32_t* d_leaf_ids_in, uint32_t n, float time_lo, float time_hi,
+               cudaStream_t stream) {
+    if (n == 0) return RT_OK;
+    cudaEvent_t ev[6];
+    for (auto& e : ev) RT_CUDA(cudaEventCreate(&e));
+    const uint32_t nblocks = (n + SORT_TILE - 1) / SORT_TILE;
+    const uint32_t tb = 256, gb = (n + tb - 1) / tb;
+
+    float4 *box_lo = nullptr, *box_hi = nullptr, *leaf_lo = nullptr, *leaf_hi = nullptr, *node_lo = nullptr, *node_hi = nullptr;
+    uint64_t *keys_a = nullptr, *keys_b = nullptr;
+    uint32_t *vals_a = nullptr, *vals_b = nullptr, *counts = nullptr, *scene_ord = nullptr, *trivial = nullptr, *visit = nullptr;
+    int *left = nullptr, *right = nullptr, *parent_internal = nullptr, *parent_leaf = nullptr;
+    RT_CUDA(dalloc(&box_lo, n)); RT_CUDA(dalloc(&box_hi, n)); RT_CUDA(dalloc(&leaf_lo, n)); RT_CUDA(dalloc(&leaf_hi, n));
+    RT_CUDA(dalloc(&node_lo, n)); RT_CUDA(dalloc(&node_hi, n));
+    RT_CUDA(dalloc(&keys_a, n)); RT_CUDA(dalloc(&keys_b, n)); RT_CUDA(dalloc(&vals_a, n)); RT_CUDA(dalloc(&vals_b, n));
+    RT_CUDA(dalloc(&counts, (size_t)256 * nblocks)); RT_CUDA(dalloc(&scene_ord, 6)); RT_CUDA(dalloc(&trivial, 1)); RT_CUDA(dalloc(&visit, n));
+    RT_CUDA(dalloc(&left, n)); RT_CUDA(dalloc(&right, n)); RT_CUDA(dalloc(&parent_internal, n)); RT_CUDA(dalloc(&parent_leaf, n));
+
+    DPrim* prims_out = nullptr; uint32_t* leaf_ids_out = nullptr; BNode* nodes = nullptr;
+    RT_CUDA(dalloc(&prims_out, n)); RT_CUDA(dalloc(&leaf_ids_out, n));
+    const uint32_t n_nodes = n > 1 ? n - 1 : 1;
+    RT_CUDA(dalloc(&nodes, n_nodes));
+
+    const uint32_t ord_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    RT_CUDA(cudaMemcpyAsync(scene_ord, ord_init, sizeof(ord_init), cudaMemcpyHostToDevice, stream));
+    RT_CUDA(cudaMemsetAsync(visit, 0, sizeof(uint32_t) * n, stream));
+
+    RT_CUDA(cudaEventRecord(ev[0], stream));
+    k_prim_bounds<<<gb, tb, 0, stream>>>(ds.view, d_prims_in, n, time_lo, time_hi, box_lo, box_hi, scene_ord);
+    k_morton<<<gb, tb, 0, stream>>>(box_lo, box_hi, n, scene_ord, keys_a, vals_a);
+    RT_CUDA(cudaEventRecord(ev[1], stream));
+    uint64_t *kin = keys_a, *kout = keys_b;
+    uint32_t *vin = vals_a, *vout = vals_b;
+    for (int pass = 0; pass < 8; pass++) {   // 63-bit codes: 8 passes of 8 bits
+        const int shift = 8 * pass;
+        k_sort_hist<<<nblocks, SORT_THREADS, 0, stream>>>(kin, n, shift, counts);
+        k_sort_scan<<<1, 1024, 0, stream>>>(counts, 256 * nblocks, nblocks, n, trivial);
+        k_sort_scatter<<<nblocks, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, counts, trivial);
+        std::swap(kin, kout); std::swap(vin, vout);
+    }
+    RT_CUDA(cudaEventRecord(ev[2], stream));
+    if (n > 1) k_karras<<<gb, tb, 0, stream>>>(kin, (int)n, left, right, parent_internal, parent_leaf);
+    RT_CUDA(cudaEventRecord(ev[3], stream));
+    k_refit<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, right, parent_internal, parent_leaf, leaf_lo, leaf_hi, node_lo, node_hi, visit);
+    RT_CUDA(cudaEventRecord(ev[4], stream));
+    k_emit_nodes<<<gb, tb, 0, stream>>>((int)n, left, right, leaf_lo, leaf_hi, node_lo, node_hi, nodes);
+    k_permute_prims<<<gb, tb, 0, stream>>>(n, vin, d_prims_in, d_leaf_ids_in, prims_out, leaf_ids_out);
+    RT_CUDA(cudaEventRecord(ev[5], stream));
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaStreamSynchronize(stream));
+
+    cudaEventElapsedTime(&ds.build.ms_morton, ev[0], ev[1]);
+    cudaEventElapsedTime(&ds.build.ms_sort, ev[1], ev[2]);
+    cudaEventElapsedTime(&ds.build.ms_hierarchy, ev[2], ev[3]);
+    cudaEventElapsedTime(&ds.build.ms_refit, ev[3], ev[4]);
+    cudaEventElapsedTime(&ds.build.ms_collapse, ev[4], ev[5]);
+    for (auto& e : ev) cudaEventDestroy(e);
+
+    ds.d_prims = prims_out; ds.d_prim_leaf_id = leaf_ids_out; ds.d_nodes = nodes;
+    ds.view.prims = prims_out; ds.view.prim_leaf_id = leaf_ids_out; ds.view.nodes = nodes;
+    ds.view.n_nodes = n_nodes;
+    ds.build.n_nodes = n_nodes;
+
+    cudaFree(box_lo); cudaFree(box_hi); cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(node_lo); cudaFree(node_hi);
+    cudaFree(keys_a); cudaFree(keys_b); cudaFree(vals_a); cudaFree(vals_b); cudaFree(counts); cudaFree(scene_ord);
+    cudaFree(trivial); cudaFree(visit); cudaFree(left); cudaFree(right); cudaFree(parent_internal); cudaFree(parent_leaf);
+    return RT_OK;
+}
+
+} // namespace rtb

@@ -1,0 +1,17 @@
+// device_scene.h — interface between the C-ABI layer (c_api.cpp) and the CUDA side (device_*.cu).
+#pragma once
+#include <string>
+#include "scene_host.h"
+
+struct rt_scene;
+
+namespace rtb {
+
+struct DeviceScene;   // defined in device_scene.cuh (CUDA translation units only)
+
+void set_error(const std::string& e);
+HostScene& host_of(rt_scene* s);
+DeviceScene*& device_of(rt_scene* s);
+void device_scene_destroy(DeviceScene* d);
+
+} // namespace rtb

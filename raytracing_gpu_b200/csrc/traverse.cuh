@@ -1,0 +1,99 @@
+// traverse.cuh — closest-hit query over the LBVH + media: what color_f asks of the world (render.h:63).
+// Replaces hittable_list::hit / bvh_node::hit (hittable_list.h:23, bvh.h:348): no device new/delete, no powf,
+// ordered descent with a shrinking t_max, one 64-byte node fetch per two child boxes.
+#pragma once
+
+#include "intersect.cuh"
+#include "rng.cuh"
+
+namespace rtb {
+
+#define RT_STACK 96   // LBVH depth bound: 63 key bits + index bits for duplicate keys
+
+struct Closest {
+    float t;     // +inf on miss
+    int prim;    // >= 0: surface primitive (device order); -1: miss; <= -2: medium index = -2 - prim
+};
+
+struct TraversalCounters { uint32_t nodes, prim_tests; };
+
+// ties: the reference's hittable_list lets the LATER object win (t == closest_so_far is accepted,
+// sphere.h:49, aarect.h:66) — with an unordered traversal that becomes "higher leaf id wins".
+__device__ __forceinline__ void consider(const SceneView& sv, int prim, float t, Closest& best) {
+    if (t < best.t || best.prim < 0 || sv.prim_leaf_id[prim] > sv.prim_leaf_id[best.prim]) { best.t = t; best.prim = prim; }
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& ray, float t_min, Closest& best, TraversalCounters* cnt) {
+    if (sv.n_prims == 0) return;
+    // slab set-up: t = plane * inv - o * inv as one FMA; zero direction components are nudged so inv stays finite
+    const float tiny = 1e-20f;
+    const float ix = 1.0f / (fabsf(ray.d.x) < tiny ? copysignf(tiny, ray.d.x) : ray.d.x);
+    const float iy = 1.0f / (fabsf(ray.d.y) < tiny ? copysignf(tiny, ray.d.y) : ray.d.y);
+    const float iz = 1.0f / (fabsf(ray.d.z) < tiny ? copysignf(tiny, ray.d.z) : ray.d.z);
+    const float ox = ray.o.x * ix, oy = ray.o.y * iy, oz = ray.o.z * iz;
+
+    // object-space ray cache: consecutive leaves usually share a wrapper chain (e.g. 1000 spheres under one)
+    uint32_t cached_chain = 0;
+    Ray cached = ray;
+
+    int stack[RT_STACK];
+    int sp = 0;
+    int node = 0;
+    for (;;) {
+        if (node >= 0) {
+            const BNode* np = sv.nodes + node;
+            const float4 n0 = __ldg(&np->n0), n1 = __ldg(&np->n1), n2 = __ldg(&np->n2);
+            const int2 ch = __ldg(reinterpret_cast<const int2*>(&np->child0));
+            if (COUNT) cnt->nodes++;
+            const float c0lox = fmaf(n0.x, ix, -ox), c0hix = fmaf(n0.y, ix, -ox), c0loy = fmaf(n0.z, iy, -oy), c0hiy = fmaf(n0.w, iy, -oy);
+            const float c1lox = fmaf(n1.x, ix, -ox), c1hix = fmaf(n1.y, ix, -ox), c1loy = fmaf(n1.z, iy, -oy), c1hiy = fmaf(n1.w, iy, -oy);
+            const float c0loz = fmaf(n2.x, iz, -oz), c0hiz = fmaf(n2.y, iz, -oz), c1loz = fmaf(n2.z, iz, -oz), c1hiz = fmaf(n2.w, iz, -oz);
+            const float t0n = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
+            const float t0f = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
+            const float t1n = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
+            const float t1f = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), best.t));
+            const bool h0 = t0n <= t0f, h1 = t1n <= t1f;
+            if (h0 && h1) {
+                const bool swap = t1n < t0n;
+                stack[sp++] = swap ? ch.x : ch.y;
+                node = swap ? ch.y : ch.x;
+                continue;
+            }
+            if (h0) { node = ch.x; continue; }
+            if (h1) { node = ch.y; continue; }
+        } else {
+            const int prim = ~node;
+            const DPrim p = sv.prims[prim];
+            const uint32_t chain = prim_chain(p);
+            if (chain != cached_chain) { cached = to_object_space(sv, chain, ray); cached_chain = chain; }
+            if (COUNT) cnt->prim_tests++;
+            float t;
+            if (prim_t_local(p, chain ? cached : ray, t_min, best.t, t)) consider(sv, prim, t, best);
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+}
+
+// Media are evaluated after the surfaces with t_max = closest surface.  In the reference a medium sees only
+// the objects listed BEFORE it (hittable_list.h:29-35); because constant_medium clips its exit to t_max before
+// sampling (constant_medium.h:44) the result is the same except where the sampled distance lands within one
+// rounding step of a later surface.  xi: scripted draw (first-hit queries) or NULL for Philox.
+template <bool COUNT>
+__device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& ray, float t_min, const RngKey* g, const float* scripted_xi,
+                                               TraversalCounters* cnt) {
+    Closest best; best.t = INFINITY; best.prim = -1;
+    closest_surface<COUNT>(sv, ray, t_min, best, cnt);
+    if (g || scripted_xi) {
+        for (uint32_t m = 0; m < sv.n_media; m++) {
+            const DMedium med = sv.media[m];
+            auto xi = [&]() { return scripted_xi ? *scripted_xi : draw4(*g, RT_STREAM_MEDIUM, m).x; };
+            float t;
+            if (medium_t(sv, med, ray, t_min, best.t, xi, t)) { best.t = t; best.prim = -2 - (int)m; }
+        }
+    }
+    return best;
+}
+
+} // namespace rtb

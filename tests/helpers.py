@@ -1,0 +1,192 @@
+"""Test helpers: loaders for the two oracles (TEST INFRASTRUCTURE under oracle/), scene programs, ray sets."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+NAMED_SCENES = ["basic", "first", "big1", "two_spheres", "two_perlin", "cornell", "cornell_smoke", "triangle", "triangles"]
+
+_oracle = None
+_ref = None
+
+
+def oracle_lib():
+    """oracle/librt_oracle.so — the plain-C restatement; built on demand (gcc only)."""
+    global _oracle
+    if _oracle is not None:
+        return _oracle
+    path = os.path.join(ORACLE_DIR, "librt_oracle.so")
+    if not os.path.exists(path):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "librt_oracle.so"])
+    L = C.CDLL(path)
+    vp = C.c_void_p
+    L.rto_scene_load.restype = vp
+    L.rto_scene_load.argtypes = [vp, C.c_size_t]
+    L.rto_scene_free.argtypes = [vp]
+    L.rto_first_hit.argtypes = [vp, vp, C.c_int, C.c_float, vp, vp, vp]
+    L.rto_philox4x32_10.argtypes = [vp, vp, vp]
+    L.rto_u01.restype = C.c_float
+    L.rto_u01.argtypes = [C.c_uint32]
+    L.rto_render_rows.restype = C.c_uint64
+    L.rto_render_rows.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32, vp]
+    L.rto_sample_radiance.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_uint32, vp, vp, C.c_int, vp, vp]
+    _oracle = L
+    return L
+
+
+def ref_lib():
+    """oracle/_ref/libref_oracle.so — the reference's own sources compiled for the host; None if absent."""
+    global _ref
+    if _ref is not None:
+        return _ref
+    path = os.path.join(ORACLE_DIR, "_ref", "libref_oracle.so")
+    if not os.path.exists(path):
+        return None
+    L = C.CDLL(path)
+    vp = C.c_void_p
+    L.ref_scene_named.argtypes = [C.c_char_p]
+    L.ref_scene_earth.argtypes = [vp, C.c_int, C.c_int, C.c_int]
+    L.ref_scene_final.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_float]
+    L.ref_scene_mesh.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp]
+    L.ref_program_words.restype = C.c_size_t
+    L.ref_aspect.restype = C.c_float
+    L.ref_first_hit.argtypes = [C.c_int, vp, C.c_int, C.c_float, vp, vp, vp, C.c_int]
+    L.ref_render.argtypes = [C.c_int] * 7 + [vp]
+    _ref = L
+    return L
+
+
+def ref_program(L, handle):
+    n = L.ref_program_words(handle)
+    prog = np.zeros(n, np.uint32)
+    L.ref_program_copy(handle, prog.ctypes.data)
+    return prog
+
+
+class OracleScene:
+    """A flattened-scene blob loaded into the C oracle."""
+
+    def __init__(self, blob):
+        self.L = oracle_lib()
+        self.blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        self.h = self.L.rto_scene_load(self.blob.ctypes.data, self.blob.size)
+        assert self.h, "oracle rejected the blob"
+
+    def first_hit(self, rays, t_min=0.001, xi=None):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 7)
+        n = rays.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        xi_a = np.ascontiguousarray(xi, np.float32) if xi is not None else None
+        self.L.rto_first_hit(self.h, rays.ctypes.data, n, t_min, xi_a.ctypes.data if xi_a is not None else None,
+                             ids.ctypes.data, t.ctypes.data)
+        return ids, t
+
+    def render(self, width, height, spp, max_depth=50, seed=1984, sample_first=0, workers=None):
+        """Mean image (H, W, 3), row 0 = bottom; rows fanned out over processes."""
+        from concurrent.futures import ThreadPoolExecutor
+        workers = workers or os.cpu_count() or 1
+        sums = np.zeros((height, width, 3), np.float32)
+        rows = [(r, min(height, r + 4)) for r in range(0, height, 4)]
+
+        def job(rr):   # ctypes releases the GIL during the call
+            return self.L.rto_render_rows(self.h, width, height, rr[0], rr[1], sample_first, spp, max_depth, seed, sums.ctypes.data)
+        with ThreadPoolExecutor(workers) as ex:
+            rays = sum(ex.map(job, rows))
+        return (np.float32(1.0) / np.float32(spp)) * sums, rays
+
+    def sample_radiance(self, width, height, pix, smp, max_depth=50, seed=1984):
+        pix = np.ascontiguousarray(pix, np.uint32)
+        smp = np.ascontiguousarray(smp, np.uint32)
+        out = np.empty((pix.size, 3), np.float32)
+        segs = np.empty(pix.size, np.uint32)
+        self.L.rto_sample_radiance(self.h, width, height, max_depth, seed, pix.ctypes.data, smp.ctypes.data, pix.size,
+                                   out.ctypes.data, segs.ctypes.data)
+        return out, segs
+
+    def __del__(self):
+        try:
+            self.L.rto_scene_free(self.h)
+        except Exception:
+            pass
+
+
+def blob_camera(blob):
+    """rt_flat_camera (24 floats) from an export blob (rt_flat_header: 80-byte prefix)."""
+    return np.frombuffer(np.ascontiguousarray(blob)[80:176].tobytes(), np.float32)
+
+
+def blob_header(blob):
+    return np.frombuffer(np.ascontiguousarray(blob)[:64].tobytes(), np.uint32)
+
+
+def make_rays(blob, n, seed):
+    """Deterministic ray set for a scene: half primary rays through random film points (random shutter time),
+    half secondary-like rays (origins jittered around the eye->scene segment, random directions)."""
+    cam = blob_camera(blob)
+    origin, llc, hor, ver = cam[0:3], cam[3:6], cam[6:9], cam[9:12]
+    rng = np.random.default_rng(seed)
+    su = rng.random(n, dtype=np.float32)
+    sv = rng.random(n, dtype=np.float32)
+    d = (llc + su[:, None] * hor + sv[:, None] * ver - origin).astype(np.float32)
+    o = np.tile(origin, (n, 1)).astype(np.float32)
+    tm = rng.random((n, 1), dtype=np.float32)
+    rays = np.concatenate([o, d, tm], axis=1).astype(np.float32)
+    h = n // 2
+    # secondary-like: start somewhere along the primary ray, head in a random direction
+    frac = rng.random((n - h, 1), dtype=np.float32)
+    rays[h:, 0:3] = rays[h:, 0:3] + frac * rays[h:, 3:6] * np.float32(0.9)
+    rays[h:, 3:6] = rng.random((n - h, 3), dtype=np.float32) - np.float32(0.5)
+    xi = (rng.random(n, dtype=np.float32) * np.float32(0.998) + np.float32(0.001)).astype(np.float32)
+    return np.ascontiguousarray(rays), xi
+
+
+def load_golden(name):
+    path = os.path.join(GOLDEN, name + ".npz")
+    return np.load(path)
+
+
+def rmse(a, b):
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return float(np.sqrt(np.mean((a - b) ** 2)))
+
+
+def procedural_image(w, h, seed=7):
+    """Synthetic RGB8 texture standing in for earthmap.jpg / mesh textures (reference assets are not copied)."""
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w].astype(np.float32)
+    img = np.stack([127 + 120 * np.sin(x * 0.021) * np.cos(y * 0.017), 127 + 120 * np.sin(x * 0.013 + y * 0.011),
+                    127 + 120 * np.cos(x * 0.007 - y * 0.019)], axis=-1)
+    img += rng.integers(-6, 7, size=img.shape)
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
+def procedural_mesh(n_theta, n_phi, seed=3):
+    """Seeded bumpy sphere mesh (stands in for the missing cup/backpack .obj): flat arrays as create_meshes_d
+    takes them (vertices 3V, indices 3T, uvs 2V, normals 3V — normals deliberately not unit length)."""
+    rng = np.random.default_rng(seed)
+    th = np.linspace(0.05, np.pi - 0.05, n_theta, dtype=np.float64)
+    ph = np.linspace(0, 2 * np.pi, n_phi, endpoint=False, dtype=np.float64)
+    T, P = np.meshgrid(th, ph, indexing="ij")
+    r = 0.5 + 0.05 * np.sin(5 * T) * np.cos(4 * P) + 0.01 * rng.random(T.shape)
+    x, y, z = r * np.sin(T) * np.cos(P), r * np.cos(T) + 0.6, r * np.sin(T) * np.sin(P)
+    verts = np.stack([x, y, z], -1).reshape(-1, 3).astype(np.float32)
+    norms = (np.stack([np.sin(T) * np.cos(P), np.cos(T), np.sin(T) * np.sin(P)], -1).reshape(-1, 3) *
+             (0.5 + rng.random((n_theta * n_phi, 1)))).astype(np.float32)
+    uvs = np.stack([P / (2 * np.pi), 1 - T / np.pi], -1).reshape(-1, 2).astype(np.float32)
+    idx = []
+    for i in range(n_theta - 1):
+        for j in range(n_phi):
+            a, b = i * n_phi + j, i * n_phi + (j + 1) % n_phi
+            c, d = a + n_phi, b + n_phi
+            idx += [a, c, b, b, c, d]
+    return verts, np.asarray(idx, np.uint32), uvs, norms
+
+
+MESH_CAMERA = np.asarray([0, 1.2, -3, 0, 0.6, 0, 0, 1, 0, 30, 16.0 / 9.0, 0.0, 10.0, 0, 1], np.float32)
