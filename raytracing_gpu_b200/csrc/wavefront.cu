@@ -318,6 +318,8 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         k_turnover<<<1, 1, 0, stream>>>(P.v, 1, 0, d_live);     // clears cursors; "cur" = the empty queue 1
         launches += 2;
         bool done = false;
+        // hard bound: every iteration with live paths retires >= 1 segment of a path of <= max_depth segments
+        const uint64_t max_iterations = (total / capacity + 2) * (uint64_t)st.max_depth + POLL_DEPTH + 64;
         for (uint64_t it = 0; !done; it++) {
             const int cur = (int)(it & 1), next = cur ^ 1;
             if (count) k_extend<true><<<P.grid_extend, BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
@@ -333,7 +335,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
                 RT_CUDA(cudaEventSynchronize(P.poll_ev[old % POLL_SLOTS]));
                 if (P.h_live[old % POLL_SLOTS] == 0) done = true;
             }
-            if (it > (1ull << 40)) break;
+            if (it > max_iterations) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
         }
     }
     RT_CUDA(cudaEventRecord(P.ev_end, stream));

@@ -190,3 +190,23 @@ def procedural_mesh(n_theta, n_phi, seed=3):
 
 
 MESH_CAMERA = np.asarray([0, 1.2, -3, 0, 0.6, 0, 0, 1, 0, 30, 16.0 / 9.0, 0.0, 10.0, 0, 1], np.float32)
+
+
+def media_leaf_ids(blob):
+    """Leaf ids of the constant_medium objects in an export blob (layout: include/rt_flat.h)."""
+    h = blob_header(blob)
+    pad16 = lambda n: (n + 15) & ~15
+    off = 176 + pad16(64 * int(h[2])) + pad16(64 * int(h[3])) + pad16(96 * int(h[4])) + pad16(16 * int(h[5])) + pad16(16 * int(h[6]))
+    n = int(h[7])
+    m = np.frombuffer(np.ascontiguousarray(blob)[off:off + 32 * n].tobytes(), np.uint32).reshape(n, 8)
+    return m[:, 4].astype(np.int32)
+
+
+def assert_first_hit_parity(blob, ids, t, want_ids, want_t):
+    """The parity bar for first-hit queries: ids exact; t bit-identical for surface hits; for constant_medium hits
+    (whose t goes through libm logf, constant_medium.h:57) within 1e-6 relative — both inside BASELINE's 1e-5."""
+    np.testing.assert_array_equal(ids, want_ids)
+    med = np.isin(ids, media_leaf_ids(blob))
+    np.testing.assert_array_equal(t[~med].view(np.uint32), want_t[~med].view(np.uint32))
+    if med.any():
+        np.testing.assert_allclose(t[med], want_t[med], rtol=1e-6, atol=0)
