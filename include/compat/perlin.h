@@ -1,0 +1,3 @@
+// Forwarding header: lets sources written against the reference's "perlin.h" build against the B200 core.
+#pragma once
+#include "rt_compat_cuda.h"

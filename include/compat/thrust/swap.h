@@ -1,0 +1,2 @@
+#pragma once
+#include "../rt_compat_cuda.h"

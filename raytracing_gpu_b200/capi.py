@@ -35,6 +35,12 @@ class BuildStats(C.Structure):
                 ("ms_collapse", C.c_float), ("ms_total", C.c_float)]
 
 
+class CatalogParams(C.Structure):
+    _fields_ = [("image", C.c_void_p), ("image_width", C.c_int), ("image_height", C.c_int), ("image_bytes_per_pixel", C.c_int),
+                ("aspect", C.c_float), ("vertices", C.c_void_p), ("n_vertices", C.c_int), ("indices", C.c_void_p),
+                ("n_triangles", C.c_int), ("uvs", C.c_void_p), ("normals", C.c_void_p), ("camera15", C.c_void_p)]
+
+
 RENDER_COUNTERS = 1
 
 _lib = None
@@ -79,6 +85,7 @@ def lib():
         "rt_render": (i32, [vp, C.POINTER(RenderSettings), vp, C.POINTER(RenderStats)]),
         "rt_render_device": (i32, [vp, C.POINTER(RenderSettings), vp, vp, C.POINTER(RenderStats)]),
         "rt_quantize_frame": (i32, [vp, i32, i32, vp]),
+        "rt_catalog_scene": (i32, [vp, C.c_char_p, C.POINTER(CatalogParams), C.POINTER(C.c_float)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)      # AttributeError here means the .so does not export a declared symbol
@@ -188,6 +195,28 @@ class Scene:
     def set_camera_raw(self, cam24):
         c = _f32(cam24).reshape(24)
         return _check(lib().rt_set_camera_raw(self._h, c.ctypes.data))
+
+    @staticmethod
+    def from_catalog(name, image=None, aspect=0.0, mesh=None, camera15=None):
+        """Library scene (include/rt_catalog.h).  image: (H, W, 3|4) uint8; mesh: (vertices, indices, uvs, normals).
+        Returns (scene, aspect_ratio)."""
+        sc = Scene()
+        p = CatalogParams()
+        keep = []
+        if image is not None:
+            img = np.ascontiguousarray(image, dtype=np.uint8)
+            keep.append(img)
+            p.image, p.image_height, p.image_width, p.image_bytes_per_pixel = img.ctypes.data, img.shape[0], img.shape[1], img.shape[2]
+        p.aspect = float(aspect)
+        if mesh is not None:
+            v, idx, uv, nrm = (_f32(mesh[0]), np.ascontiguousarray(mesh[1], dtype=np.uint32), _f32(mesh[2]), _f32(mesh[3]))
+            cam = _f32(camera15)
+            keep += [v, idx, uv, nrm, cam]
+            p.vertices, p.n_vertices, p.indices, p.n_triangles = v.ctypes.data, v.size // 3, idx.ctypes.data, idx.size // 3
+            p.uvs, p.normals, p.camera15 = uv.ctypes.data, nrm.ctypes.data, cam.ctypes.data
+        a = C.c_float()
+        _check(lib().rt_catalog_scene(sc._h, name.encode(), C.byref(p), C.byref(a)))
+        return sc, a.value
 
     # ---- helpers with array arguments -----------------------------------------------------------
     def replay(self, program):
