@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py — path-tracing throughput (Msamples/s) of the B200-native core on the reference's headline scene.
+
+One "step" = one full pass of the hot path over one frame: clear the accumulation buffer, run the wavefront
+pipeline (generate / extend / shade) over every sample of the frame, (N > 1: one NCCL reduce of the float
+accumulation buffers,) scale by 1/spp.
+
+Workload (config.workload): BASELINE.json config 3, the Next-Week final scene, 1920 x 1079 (the height the
+reference computes for 1920 at 16:9, render.h:33), 1024 samples per pixel PER GPU, max depth 50 — weak scaling:
+at N GPUs the frame has 1024*N spp, sample-split, rank r renders samples [1024 r, 1024 (r+1)).
+The earth texture is synthetic (reference assets are not redistributed); all other scene data is the scene itself.
+
+  value      whole-job Msamples/s, scene resident in HBM, CUDA events, max over ranks
+  e2e        same metric through the C-ABI with host buffers: rt_scene_commit (H2D of the flattened scene + GPU
+             LBVH build) + render + reduce + D2H of the W*H*3 float image, every step
+  roofline   dominant kernel (extend): algorithmic 48 B per ray segment / its CUDA-event time vs measured HBM copy
+             bandwidth; the binding roofline (FP32 issue) is reported next to it as roofline_fp32
+  cpu_baseline / --impl reference
+             the reference's own render()/color_f() (oracle/_ref, its sources compiled for the host) on the box's
+             host cores, on a bounded sample of the same frame
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED = 1984
+WORKLOADS = {
+    # name: (catalog scene, width, aspect, spp per GPU, description)
+    "final": ("final", 1920, 16.0 / 9.0, 1024, "Next-Week final scene 1920x1079 1024spp/GPU depth50 (BASELINE config 3)"),
+    "cornell_smoke": ("cornell_smoke", 800, 1.0, 1024, "Cornell box with smoke 800x800 1024spp/GPU depth50 (BASELINE config 2)"),
+    "big1": ("big1", 400, 16.0 / 9.0, 16, "RTIOW random spheres 400x224 16spp depth50 (BASELINE config 1)"),
+    "mesh": ("mesh", 1920, 16.0 / 9.0, 256, "procedural 1M-triangle mesh + ground 1920x1079 256spp/GPU (BASELINE config 4 stand-in)"),
+}
+
+
+def synthetic_earth(w=3410, h=1518):
+    """Stand-in for textures/earthmap.jpg (same size): smooth continents + noise, RGB8."""
+    rng = np.random.default_rng(2026)
+    y, x = np.mgrid[0:h, 0:w].astype(np.float32)
+    land = np.sin(x * 0.004) * np.cos(y * 0.006) + 0.5 * np.sin(x * 0.013 + y * 0.009)
+    img = np.empty((h, w, 3), np.float32)
+    img[..., 0] = np.where(land > 0.2, 90 + 60 * land, 20)
+    img[..., 1] = np.where(land > 0.2, 120 + 40 * land, 60 + 30 * land)
+    img[..., 2] = np.where(land > 0.2, 60, 150 + 40 * land)
+    img += rng.integers(-8, 9, size=img.shape)
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
+def big_mesh(n_theta=708, n_phi=708):
+    """~1M-triangle seeded procedural mesh (stands in for the missing cup/backpack .obj)."""
+    from tests import helpers
+    return helpers.procedural_mesh(n_theta, n_phi, seed=3)
+
+
+def build_scene(rt, name, aspect):
+    if name == "final":
+        return rt.Scene.from_catalog("final", image=synthetic_earth(), aspect=float(np.float32(aspect)))
+    if name == "mesh":
+        from tests import helpers
+        img = np.asarray(helpers.procedural_image(2048, 2048, seed=13))
+        return rt.Scene.from_catalog("mesh", image=img, mesh=big_mesh(), camera15=helpers.MESH_CAMERA)
+    return rt.Scene.from_catalog(name)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in self.rows if len(r) >= 6 for k in range(4) if r[2 + k].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return json.load(open(path)), "measured"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+# --------------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's own CPU-compiled render() on the host cores
+# --------------------------------------------------------------------------------------------------------------
+def reference_cpu(workload, steps, warmup, budget_s=12.0):
+    """Times oracle/_ref (kind "reference") — or, where it was never built, the C restatement (kind "port") — on a
+    bounded sample of the workload: the full-resolution frame at a reduced sample count."""
+    from tests import helpers
+    import raytracing_gpu_b200 as rt
+    scene_name, width, aspect, spp, desc = WORKLOADS[workload]
+    cores = os.cpu_count() or 1
+    L = helpers.ref_lib()
+    height = rt.image_height(width, np.float32(aspect))
+    if L is not None:
+        if scene_name == "final":
+            img = synthetic_earth()
+            h = L.ref_scene_final(img.ctypes.data, img.shape[1], img.shape[0], 3, C.c_float(np.float32(aspect)))
+        elif scene_name == "mesh":
+            v, idx, uv, nrm = big_mesh(180, 180)   # the reference's one-thread O(n^2) BVH build cannot take 1M triangles
+            img = np.asarray(helpers.procedural_image(2048, 2048, seed=13))
+            h = L.ref_scene_mesh(v.ctypes.data, len(v), idx.ctypes.data, len(idx) // 3, uv.ctypes.data, nrm.ctypes.data,
+                                 img.ctypes.data, 2048, 2048, 3, helpers.MESH_CAMERA.ctypes.data)
+        else:
+            h = L.ref_scene_named(scene_name.encode())
+        fb = np.zeros((height, width, 3), np.float32)
+        times = (C.c_double * 2)()
+
+        def run(ns):
+            L.ref_render(h, width, height, ns, 50, 0, cores, fb.ctypes.data)
+            L.ref_last_times(times)
+            return times[1]          # the render pass only; render_init is excluded like on the GPU side
+        kind = "reference"
+    else:
+        sc, _ = build_scene(rt, scene_name, aspect)
+        o = helpers.OracleScene(sc.export())
+
+        def run(ns):
+            t0 = time.time()
+            o.render(width, height, ns, seed=SEED, workers=cores)
+            return time.time() - t0
+        kind = "port"
+    t1 = run(1)                                            # calibration pass (also the warm-up)
+    ns = int(max(1, min(spp, budget_s / max(t1, 1e-3) / max(1, steps + warmup))))
+    for _ in range(max(0, warmup - 1)):
+        run(ns)
+    ts = [run(ns) for _ in range(steps)]
+    t = float(np.mean(ts))
+    value = width * height * ns / t / 1e6
+    sample = f"{width}x{height} full frame, {ns} of {spp} spp, depth 50, render pass only, {cores} host threads"
+    return {"value": value, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": sample}, t * 1e3
+
+
+def print_reference_line(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    scene_name, width, aspect, spp, desc = WORKLOADS[args.workload]
+    cb, ms = reference_cpu(args.workload, args.steps, args.warmup, budget_s=60.0)
+    line = {"impl": "reference", "metric": "Msamples/s", "value": cb["value"], "unit": "Msamples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "note": "reference's own render()/color_f() compiled for the host (oracle/_ref); CPU only"},
+            "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------------------------------
+# product arm
+# --------------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="final", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--pool", type=int, default=0, help="wavefront pool size in paths (0 = library default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        print_reference_line(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import raytracing_gpu_b200 as rt
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    scene_name, width, aspect, spp, desc = WORKLOADS[args.workload]
+    width = args.width or width
+    spp = args.spp or spp
+    height = rt.image_height(width, np.float32(aspect))
+    total_spp = spp * world
+    npix = width * height
+
+    sc, _ = build_scene(rt, scene_name, aspect)
+    build = sc.commit(local)
+    blob_bytes = int(len(sc.export()))
+    stream = torch.cuda.current_stream().cuda_stream
+    accum = torch.zeros(height, width, 3, device=dev, dtype=torch.float32)
+    out = torch.empty_like(accum)
+    host_img = torch.empty(height, width, 3, dtype=torch.float32).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(flags=0):
+        accum.zero_()
+        st = sc.render_device(accum.data_ptr(), width, height, total_spp, max_depth=50, seed=SEED, sample_first=rank * spp,
+                              sample_count=spp, flags=flags, pool_paths=args.pool, stream=stream)
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        torch.mul(accum, 1.0 / total_spp, out=out)
+        return st
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res = [fn() for _ in range(k)]
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), res
+
+    for _ in range(args.warmup):
+        step()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms_total, stats = timed(step, args.steps)
+    clk = clocks.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    value = npix * total_spp / (ms_step * 1e-3) / 1e6
+    rays = torch.tensor([float(np.mean([s.rays for s in stats]))], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(rays)
+    rays_per_step = float(rays.item())
+    launches = int(sum(s.kernel_launches for s in stats)) + 2 * args.steps      # + zero + scale kernels per step
+
+    # dominant kernel (extend): separate pass with per-kernel CUDA events (not part of the timed region above)
+    _, tstats = timed(lambda: step(flags=2), 1)
+    ts = tstats[0]
+    ext_launches = int(ts.iterations)
+    ext_ms = ts.ms_extend / max(ext_launches, 1)
+    ext_bytes = 48.0 * ts.rays / max(ext_launches, 1)                 # ray 32 B in + hit 16 B out per segment
+    peaks, peak_src = measured_peaks()
+    achieved = ext_bytes / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(args.workload, {}).get("extend_dram_bytes_per_launch")
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                "traffic": traffic, "kernel": "k_extend", "peak_source": peak_src, "launches_per_step": ext_launches,
+                "avg_launch_ms": ext_ms, "share_of_step": ts.ms_extend / max(ts.ms_total, 1e-9),
+                "kernel_ms_per_step": {"extend": ts.ms_extend, "shade": ts.ms_shade, "generate": ts.ms_generate, "turnover": ts.ms_finish}}
+    # FP32 roofline (the binding one): algorithmic flops from measured traversal counters (SURVEY §8d figures)
+    _, cstats = timed(lambda: step(flags=1), 1)
+    cs = cstats[0]
+    flops = 24.0 * 2 * cs.nodes_visited + 45.0 * cs.prim_tests + 55.0 * cs.rays
+    fp32_peak = 148 * 128 * 2 * (peaks.get("sm_max_mhz", 1965.0) * 1e6) / 1e12
+    roofline_fp32 = {"bound": "fp32", "achieved": flops / (ms_step * 1e-3) / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": flops / (ms_step * 1e-3) / 1e12 / fp32_peak, "peak_source": "nominal 148 SM x 128 lanes x 2 x max SM clock",
+                     "nodes_per_ray": cs.nodes_visited / max(cs.rays, 1), "prim_tests_per_ray": cs.prim_tests / max(cs.rays, 1),
+                     "rays_per_sample": cs.rays / max(cs.samples, 1)}
+
+    # end to end through the C-ABI with host buffers: commit (H2D + LBVH build) + render + reduce + D2H
+    e2e = None
+    if not args.no_e2e:
+        def e2e_step():
+            sc.commit(local)
+            step()
+            if rank == 0:
+                host_img.copy_(out, non_blocking=True)
+        e2e_step()
+        ms_e2e, _ = timed(e2e_step, args.steps)
+        image_bytes = sum(int(w) * int(h) * 4 for w, h in [(3410, 1518)]) if scene_name == "final" else 0
+        e2e = {"value": npix * total_spp / (ms_e2e / args.steps * 1e-3) / 1e6, "unit": "Msamples/s",
+               "h2d_bytes_per_step": blob_bytes + image_bytes, "d2h_bytes_per_step": npix * 12,
+               "includes": "rt_scene_commit (scene H2D + GPU LBVH build) + render + reduce + image D2H"}
+
+    cb = None
+    if rank == 0 and not args.no_cpu_baseline:
+        cb, _ = reference_cpu(args.workload, 1, 1)
+
+    if rank == 0:
+        line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": desc, "width": width, "height": height, "spp_per_gpu": spp, "spp_total": total_spp,
+                           "max_depth": 50, "partition": f"sample-split x{world} + one NCCL reduce" if world > 1 else "single GPU",
+                           "l2": "working set (pool + queues) > L2; accumulation buffer re-zeroed each step",
+                           "prims": int(build.n_prims), "bvh_nodes": int(build.n_nodes), "bvh_build_ms": float(build.ms_total)},
+                "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays_per_step / (npix * total_spp),
+                "gpu_launches": launches, "clocks": clk, "roofline": roofline, "roofline_fp32": roofline_fp32, "e2e": e2e,
+                "cpu_baseline": cb}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

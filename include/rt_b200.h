@@ -115,7 +115,8 @@ int rt_first_hit(rt_scene* s, const float* rays, int n, float t_min, const float
 
 enum rt_render_flags {
     RT_RENDER_DEFAULT = 0,
-    RT_RENDER_COUNTERS = 1  /* fill the traversal counters in rt_render_stats (slower) */
+    RT_RENDER_COUNTERS = 1, /* fill the traversal counters in rt_render_stats (slower) */
+    RT_RENDER_TIMERS = 2    /* CUDA-event time per kernel class (ms_extend / ms_shade / ms_generate / ms_finish) */
 };
 
 typedef struct rt_render_settings {  /* replaces render_settings (render.h:21-50) */

@@ -22,6 +22,7 @@
 #include <thread>
 #include <atomic>
 #include <new>
+#include <chrono>
 
 #define REF_API extern "C" __attribute__((visibility("default")))
 
@@ -440,6 +441,10 @@ REF_API void ref_first_hit(int h, const float* rays, int n, float t_min, const f
  * CUDA thread per pixel (blockDim = 1x1, blockIdx = pixel).  fb: width*height*3 floats, row 0 = bottom.
  * `batch_id` is render()'s `id` argument (render.h:101).  The camera's shared-state race is kept:
  * worker threads really do share rand_state[0]. Returns 0. */
+static double g_last_init_s = 0, g_last_render_s = 0;
+/* wall-clock seconds of the last ref_render call: [0] = render_init pass, [1] = render pass */
+REF_API void ref_last_times(double* out) { out[0] = g_last_init_s; out[1] = g_last_render_s; }
+
 REF_API int ref_render(int h, int width, int height, int ns, int max_depth, int batch_id, int nthreads, float* fb_out) {
     scene* s = g_scenes[h]->sc;
     const size_t npix = (size_t)width * height;
@@ -466,8 +471,13 @@ REF_API int ref_render(int h, int width, int height, int ns, int max_depth, int 
             });
         for (auto& t : pool) t.join();
     };
+    const auto t0 = std::chrono::steady_clock::now();
     run_rows(true);
+    const auto t1 = std::chrono::steady_clock::now();
     run_rows(false);
+    const auto t2 = std::chrono::steady_clock::now();
+    g_last_init_s = std::chrono::duration<double>(t1 - t0).count();
+    g_last_render_s = std::chrono::duration<double>(t2 - t1).count();
     free(states);
     return 0;
 }

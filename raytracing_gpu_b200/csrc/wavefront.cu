@@ -56,6 +56,7 @@ struct RenderPool {
     cudaEvent_t poll_ev[POLL_SLOTS]{};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     int grid_extend = 0, grid_shade = 0, grid_gen = 0;
+    std::vector<cudaEvent_t> timer_ev;   // RT_RENDER_TIMERS: 4 events per iteration, reused across frames
 };
 
 void render_pool_destroy(RenderPool* p) {
@@ -67,6 +68,7 @@ void render_pool_destroy(RenderPool* p) {
     for (auto& e : p->poll_ev) if (e) cudaEventDestroy(e);
     if (p->ev_begin) cudaEventDestroy(p->ev_begin);
     if (p->ev_end) cudaEventDestroy(p->ev_end);
+    for (auto& e : p->timer_ev) cudaEventDestroy(e);
     delete p;
 }
 
@@ -305,6 +307,14 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     if (!ds.pool) { const int rc = pool_create(ds, capacity); if (rc < 0) return rc; }
     RenderPool& P = *ds.pool;
     const bool count = (st.flags & RT_RENDER_COUNTERS) != 0;
+    const bool timers = (st.flags & RT_RENDER_TIMERS) != 0;
+    size_t n_timer = 0;
+    auto tick = [&]() -> int {   // records the next timer event on the stream
+        if (!timers) return RT_OK;
+        if (n_timer == P.timer_ev.size()) { cudaEvent_t e; RT_CUDA(cudaEventCreate(&e)); P.timer_ev.push_back(e); }
+        RT_CUDA(cudaEventRecord(P.timer_ev[n_timer++], stream));
+        return RT_OK;
+    };
 
     FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, 0u, total, d_accum};
     uint64_t launches = 0, iterations = 0;
@@ -322,10 +332,14 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         const uint64_t max_iterations = (total / capacity + 2) * (uint64_t)st.max_depth + POLL_DEPTH + 64;
         for (uint64_t it = 0; !done; it++) {
             const int cur = (int)(it & 1), next = cur ^ 1;
+            if (tick() < 0) return RT_ERR_CUDA;
             if (count) k_extend<true><<<P.grid_extend, BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
             else k_extend<false><<<P.grid_extend, BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            if (tick() < 0) return RT_ERR_CUDA;
             k_shade<<<P.grid_shade, BLOCK, 0, stream>>>(ds.view, P.v, fp, next);
+            if (tick() < 0) return RT_ERR_CUDA;
             k_generate<<<P.grid_gen, BLOCK, 0, stream>>>(ds.view, P.v, fp, next, false);
+            if (tick() < 0) return RT_ERR_CUDA;
             k_turnover<<<1, 1, 0, stream>>>(P.v, cur, next, d_live + (it % POLL_SLOTS));
             RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
             launches += 4;
@@ -351,6 +365,18 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         stats->nodes_visited = P.h_counters->nodes;
         stats->prim_tests = P.h_counters->prim_tests;
         cudaEventElapsedTime(&stats->ms_total, P.ev_begin, P.ev_end);
+        if (timers) {   // per-kernel device time, summed over the iterations of this frame
+            double ext = 0, shd = 0, gen = 0, fin = 0;
+            for (size_t k = 0; k + 3 < n_timer; k += 4) {
+                float a = 0, b = 0, c = 0;
+                cudaEventElapsedTime(&a, P.timer_ev[k], P.timer_ev[k + 1]);
+                cudaEventElapsedTime(&b, P.timer_ev[k + 1], P.timer_ev[k + 2]);
+                cudaEventElapsedTime(&c, P.timer_ev[k + 2], P.timer_ev[k + 3]);
+                ext += a; shd += b; gen += c;
+                if (k + 4 < n_timer) { float d = 0; cudaEventElapsedTime(&d, P.timer_ev[k + 3], P.timer_ev[k + 4]); fin += d; }
+            }
+            stats->ms_extend = (float)ext; stats->ms_shade = (float)shd; stats->ms_generate = (float)gen; stats->ms_finish = (float)fin;
+        }
     }
     return RT_OK;
 }
