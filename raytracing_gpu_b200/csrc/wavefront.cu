@@ -4,10 +4,12 @@
 //   extend    persistent warps pull 32 queued paths at a time, traverse the LBVH + media, write the hit, and append
 //             the path to the shade queue of its material class (warp-ballot aggregated appends)
 //   shade     one launch over all material queues; each warp works inside ONE queue, so a warp shades one
-//             material class; terminated paths add thr*L to the accumulation buffer (float atomics) and hand
-//             their slot to the regeneration queue, survivors are appended to the next extend queue
-//   generate  regenerated slots fetch the next (pixel, sample) from a global counter and start a camera path
+//             material class; terminated paths add thr*L to the accumulation buffer (float atomics) and are
+//             REGENERATED in place: the slot fetches the next (pixel, sample) from a global cursor (one atomic
+//             per warp) and starts a new camera path; survivors and regenerated paths are appended to the next
+//             extend queue (warp-ballot compaction)
 //   turnover  a one-thread kernel that rolls queue counters over and publishes the live-path count
+// (generate, the camera ray-generation kernel, fills the pool once at the start of a frame.)
 // The pool stays full until the samples run out, so kernels stay large; no host synchronisation inside the loop
 // (the host polls a pinned counter a few iterations behind).
 #include "device_scene.h"
@@ -43,7 +45,6 @@ struct PoolView {
     uint2* pid;        // pixel, sample | bounce << 24
     uint32_t* q_extend[2];
     uint32_t* q_shade; // NQ * capacity
-    uint32_t* q_new;
     Counters* c;
     uint32_t capacity;
 };
@@ -62,7 +63,7 @@ struct RenderPool {
 void render_pool_destroy(RenderPool* p) {
     if (!p) return;
     cudaFree(p->v.ray_o); cudaFree(p->v.ray_d); cudaFree(p->v.hit_prim); cudaFree(p->v.thr); cudaFree(p->v.pid);
-    cudaFree(p->v.q_extend[0]); cudaFree(p->v.q_extend[1]); cudaFree(p->v.q_shade); cudaFree(p->v.q_new); cudaFree(p->v.c);
+    cudaFree(p->v.q_extend[0]); cudaFree(p->v.q_extend[1]); cudaFree(p->v.q_shade); cudaFree(p->v.c);
     if (p->h_live) cudaFreeHost(p->h_live);
     if (p->h_counters) cudaFreeHost(p->h_counters);
     for (auto& e : p->poll_ev) if (e) cudaEventDestroy(e);
@@ -79,6 +80,7 @@ struct FrameParams {
     uint32_t sample_first;
     uint32_t pad;
     unsigned long long total_samples;   // samples this call renders = npix * sample_count
+    unsigned long long npix, npix_magic; // frame size and ceil(2^64 / npix)
     float* accum;                       // width*height*3 sums
 };
 
@@ -102,38 +104,57 @@ __device__ __forceinline__ uint32_t warp_claim(uint32_t* cursor) {
     return __shfl_sync(0xffffffffu, base, 0);
 }
 
-// ---- generate -------------------------------------------------------------------------------------
-// first == true: slots [0, capacity) are all free (start of a frame); otherwise slots come from q_new.
-__global__ void __launch_bounds__(BLOCK) k_generate(SceneView sv, PoolView pv, FrameParams fp, int next, bool first) {
-    const uint32_t n = first ? pv.capacity : pv.c->n_new;
+// g -> (pixel, sample): g = sample * npix + pixel.  Division by the frame size through a precomputed 64-bit
+// reciprocal (one mul.hi + a fix-up) instead of a 64-bit divide per path.
+__device__ __forceinline__ void split_sample_index(const FrameParams& fp, unsigned long long g, uint32_t& pixel, uint32_t& sample) {
+    if (fp.npix == 1) { pixel = 0; sample = fp.sample_first + (uint32_t)g; return; }
+    unsigned long long q = __umul64hi(g, fp.npix_magic);
+    long long r = (long long)(g - q * fp.npix);
+    if (r < 0) { q--; r += (long long)fp.npix; }
+    else if (r >= (long long)fp.npix) { q++; r -= (long long)fp.npix; }
+    pixel = (uint32_t)r;
+    sample = fp.sample_first + (uint32_t)q;
+}
+
+// camera ray generation for one slot (render.h:105-108)
+__device__ __forceinline__ void start_path(const SceneView& sv, const PoolView& pv, const FrameParams& fp, uint32_t slot, unsigned long long g) {
+    uint32_t pixel, sample;
+    split_sample_index(fp, g, pixel, sample);
+    const RngKey key{pixel, sample, 0u, fp.seed};
+    const uint32_t py = pixel / fp.width, px = pixel - py * fp.width;
+    const Ray r = camera_ray(sv.camera, key, (int)px, (int)py, (int)fp.width, (int)fp.height);
+    pv.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.tm);
+    pv.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
+    pv.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+    pv.pid[slot] = make_uint2(pixel, sample);   // bounce 0
+}
+
+// lanes with `want` claim consecutive global sample indices: one 64-bit atomic per warp
+__device__ __forceinline__ unsigned long long claim_samples(bool want, unsigned long long* cursor) {
+    const uint32_t mask = __ballot_sync(0xffffffffu, want);
+    if (!mask) return ~0ull;
     const uint32_t lane = threadIdx.x & 31;
-    const unsigned long long npix = (unsigned long long)fp.width * fp.height;
+    const int leader = __ffs(mask) - 1;
+    unsigned long long g0 = 0;
+    if ((int)lane == leader) g0 = atomicAdd(cursor, (unsigned long long)__popc(mask));
+    g0 = __shfl_sync(0xffffffffu, g0, leader);
+    return g0 + __popc(mask & ((1u << lane) - 1u));
+}
+
+// ---- generate -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BLOCK) k_generate(SceneView sv, PoolView pv, FrameParams fp, int next) {
+    // start of a frame: every slot [0, capacity) is free
+    const uint32_t n = pv.capacity;
+    const uint32_t lane = threadIdx.x & 31;
     for (;;) {
         const uint32_t base = warp_claim(&pv.c->cur_new);
         if (base >= n) break;
-        const uint32_t idx = base + lane;
-        const bool have_slot = idx < n;
-        const uint32_t slot = have_slot ? (first ? idx : pv.q_new[idx]) : 0;
-        // one atomic per warp on the global sample cursor
-        const uint32_t mask = __ballot_sync(0xffffffffu, have_slot);
-        unsigned long long g0 = 0;
-        if (lane == 0) g0 = atomicAdd(&pv.c->next_sample, (unsigned long long)__popc(mask));
-        g0 = __shfl_sync(0xffffffffu, g0, 0);
-        const unsigned long long g = g0 + __popc(mask & ((1u << lane) - 1u));
+        const uint32_t slot = base + lane;
+        const bool have_slot = slot < n;
+        const unsigned long long g = claim_samples(have_slot, &pv.c->next_sample);
         const bool live = have_slot && g < fp.total_samples;
-        if (live) {
-            const uint32_t pixel = (uint32_t)(g % npix);
-            const uint32_t sample = fp.sample_first + (uint32_t)(g / npix);
-            const RngKey key{pixel, sample, 0u, fp.seed};
-            const Ray r = camera_ray(sv.camera, key, (int)(pixel % fp.width), (int)(pixel / fp.width), (int)fp.width, (int)fp.height);
-            pv.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.tm);
-            pv.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
-            pv.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-            pv.pid[slot] = make_uint2(pixel, sample);   // bounce 0
-        }
+        if (live) start_path(sv, pv, fp, slot, g);
         warp_append(live, pv.q_extend[next], &pv.c->n_extend[next], slot);
-        const uint32_t lm = __ballot_sync(0xffffffffu, live);
-        if (lane == 0 && lm) atomicAdd(&pv.c->started, (unsigned long long)__popc(lm));
     }
 }
 
@@ -237,8 +258,10 @@ __global__ void __launch_bounds__(BLOCK) k_shade(SceneView sv, PoolView pv, Fram
                 }
             }
         }
+        // regeneration: a terminated path's slot immediately starts the next camera sample (if any are left)
+        const unsigned long long g = claim_samples(terminated, &pv.c->next_sample);
+        if (terminated && g < fp.total_samples) { start_path(sv, pv, fp, slot, g); continues = true; }
         warp_append(continues, pv.q_extend[next], &pv.c->n_extend[next], slot);
-        warp_append(terminated, pv.q_new, &pv.c->n_new, slot);
     }
 }
 
@@ -270,7 +293,6 @@ int pool_create(DeviceScene& ds, uint32_t capacity) {
     RT_CUDA(cudaMalloc(&p->v.q_extend[0], sizeof(uint32_t) * capacity));
     RT_CUDA(cudaMalloc(&p->v.q_extend[1], sizeof(uint32_t) * capacity));
     RT_CUDA(cudaMalloc(&p->v.q_shade, sizeof(uint32_t) * (size_t)capacity * NQ));
-    RT_CUDA(cudaMalloc(&p->v.q_new, sizeof(uint32_t) * capacity));
     RT_CUDA(cudaMalloc(&p->v.c, sizeof(Counters)));
     RT_CUDA(cudaHostAlloc(&p->h_live, sizeof(uint32_t) * POLL_SLOTS, cudaHostAllocMapped));
     RT_CUDA(cudaHostAlloc(&p->h_counters, sizeof(Counters), cudaHostAllocDefault));
@@ -316,13 +338,14 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         return RT_OK;
     };
 
-    FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, 0u, total, d_accum};
+    const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
+    FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, 0u, total, npix, magic, d_accum};
     uint64_t launches = 0, iterations = 0;
     RT_CUDA(cudaMemsetAsync(P.v.c, 0, sizeof(Counters), stream));
     RT_CUDA(cudaEventRecord(P.ev_begin, stream));
     if (total > 0) {
         // frame start: fill the pool
-        k_generate<<<P.grid_gen, BLOCK, 0, stream>>>(ds.view, P.v, fp, 0, true);
+        k_generate<<<P.grid_gen, BLOCK, 0, stream>>>(ds.view, P.v, fp, 0);
         uint32_t* d_live = nullptr;
         RT_CUDA(cudaHostGetDevicePointer(&d_live, P.h_live, 0));
         k_turnover<<<1, 1, 0, stream>>>(P.v, 1, 0, d_live);     // clears cursors; "cur" = the empty queue 1
@@ -338,11 +361,10 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
             if (tick() < 0) return RT_ERR_CUDA;
             k_shade<<<P.grid_shade, BLOCK, 0, stream>>>(ds.view, P.v, fp, next);
             if (tick() < 0) return RT_ERR_CUDA;
-            k_generate<<<P.grid_gen, BLOCK, 0, stream>>>(ds.view, P.v, fp, next, false);
             if (tick() < 0) return RT_ERR_CUDA;
             k_turnover<<<1, 1, 0, stream>>>(P.v, cur, next, d_live + (it % POLL_SLOTS));
             RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
-            launches += 4;
+            launches += 3;
             iterations++;
             if (it >= POLL_DEPTH) {
                 const uint64_t old = it - POLL_DEPTH;
@@ -358,7 +380,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     RT_CUDA(cudaGetLastError());
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
-        stats->samples = P.h_counters->started;
+        stats->samples = std::min<unsigned long long>(P.h_counters->next_sample, total);
         stats->rays = P.h_counters->total_rays;
         stats->iterations = iterations;
         stats->kernel_launches = launches;
