@@ -199,6 +199,7 @@ def main():
     import torch
     import torch.distributed as dist
     import raytracing_gpu_b200 as rt
+    from raytracing_gpu_b200.parallel import sample_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -233,8 +234,9 @@ def main():
 
     def step(flags=0):
         accum.zero_()
-        st = sc.render_device(accum.data_ptr(), width, height, total_spp, max_depth=50, seed=SEED, sample_first=rank * spp,
-                              sample_count=spp, flags=flags, pool_paths=args.pool, stream=stream)
+        first, count = sample_range(total_spp, world, rank)
+        st = sc.render_device(accum.data_ptr(), width, height, total_spp, max_depth=50, seed=SEED, sample_first=first,
+                              sample_count=count, flags=flags, pool_paths=args.pool, stream=stream)
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
         torch.mul(accum, 1.0 / total_spp, out=out)

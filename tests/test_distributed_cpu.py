@@ -1,0 +1,53 @@
+"""World-size-2 test of the multi-GPU host logic on CPU (gloo): sample-split + one sum-reduce.  The per-rank render
+is done by the C oracle (test infrastructure) because there is no GPU here; on the B200 box the same
+render_distributed() drives Scene.render_device (see bench.py)."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import raytracing_gpu_b200 as rt
+from raytracing_gpu_b200.parallel import render_distributed, sample_range
+from tests import helpers
+
+W, H, SPP = 24, 24, 7
+
+
+def test_sample_ranges_partition_exactly():
+    for spp in (1, 7, 16, 1024, 4097):
+        for world in (1, 2, 3, 4, 8):
+            seen = []
+            for r in range(world):
+                f, c = sample_range(spp, world, r)
+                seen += list(range(f, f + c))
+            assert seen == list(range(spp))
+
+
+def _worker(rank, world, port, blob, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    o = helpers.OracleScene(blob)
+
+    def render_sums(first, count, accum):
+        mean, _ = o.render(W, H, count, sample_first=first, workers=1)
+        accum += torch.from_numpy(mean * np.float32(count))
+    img = render_distributed(render_sums, H, W, SPP, torch.device("cpu"))
+    if rank == 0:
+        np.save(out_path, img.numpy())
+    dist.destroy_process_group()
+
+
+def test_two_rank_sample_split_equals_single_rank(tmp_path):
+    g = helpers.load_golden("cornell_smoke")
+    sc = rt.Scene(); sc.replay(g["program"])
+    blob = sc.export()
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    out = str(tmp_path / "img.npy")
+    mp.spawn(_worker, args=(2, port, blob, out), nprocs=2, join=True)
+    two = np.load(out)
+    one, _ = helpers.OracleScene(blob).render(W, H, SPP)
+    np.testing.assert_allclose(two, one, rtol=2e-5, atol=1e-6)
