@@ -23,7 +23,7 @@ void device_scene_destroy(DeviceScene* d) {
     if (d->device >= 0) cudaSetDevice(d->device);
     if (d->pool) render_pool_destroy(d->pool);
     void* ptrs[] = {d->d_prims, d->d_prim_leaf_id, d->d_bprims, d->d_media, d->d_tri_attrs, d->d_xops, d->d_chains,
-                    d->d_materials, d->d_textures, d->d_perlins, d->d_images, d->d_nodes};
+                    d->d_materials, d->d_textures, d->d_perlins, d->d_images, d->d_nodes, d->d_active_media};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (uint32_t i = 0; i < d->n_images; i++) {
         if (d->image_objs && d->image_objs[i]) cudaDestroyTextureObject(d->image_objs[i]);
@@ -76,6 +76,17 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
         const rt_flat_medium& m = fs.media[i];
         media[i] = DMedium{m.chain, m.bprim_first, m.bprim_count, m.material, m.leaf_id, m.neg_inv_density, 0, 0};
     }
+    // A constant_medium whose boundary is ONE sphere can never report a hit under the reference's semantics
+    // (SURVEY Q1/Q2): its second boundary query (constant_medium.h:39, t_min = t1 + 0.0001) meets the same near
+    // root t1 again, which is either rejected (t1 < t_min) or accepted as t2 == t1 and then dropped by
+    // `t1 >= t2` (:46).  Such media are left out of the per-ray loop; indices (RNG blocks, hit encoding) keep
+    // counting all media, so results are unchanged.
+    std::vector<uint32_t> active_media;
+    for (size_t i = 0; i < fs.media.size(); i++) {
+        const rt_flat_medium& m = fs.media[i];
+        const bool inert = m.bprim_count == 1 && (fs.bprims[m.bprim_first].type == RT_PRIM_SPHERE || fs.bprims[m.bprim_first].type == RT_PRIM_MOVING_SPHERE);
+        if (!inert) active_media.push_back((uint32_t)i);
+    }
     std::vector<DPerlin> perlins(fs.perlins.size());
     for (size_t i = 0; i < fs.perlins.size(); i++) {
         for (int k = 0; k < 256; k++) perlins[i].ranvec[k] = make_float4(fs.perlins[i].ranvec[3 * k], fs.perlins[i].ranvec[3 * k + 1], fs.perlins[i].ranvec[3 * k + 2], 0.f);
@@ -112,6 +123,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     if ((rc = upload(&d_leaf_in, leaf_ids, st)) < 0) return rc;
     if ((rc = upload(&ds.d_bprims, bprims, st)) < 0) return rc;
     if ((rc = upload(&ds.d_media, media, st)) < 0) return rc;
+    if ((rc = upload(&ds.d_active_media, active_media, st)) < 0) return rc;
     if ((rc = upload(&ds.d_tri_attrs, fs.tri_attrs, st)) < 0) return rc;
     if ((rc = upload(&ds.d_xops, fs.xops, st)) < 0) return rc;
     if ((rc = upload(&ds.d_chains, fs.chains, st)) < 0) return rc;
@@ -127,6 +139,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     v.textures = (const rt_flat_texture*)ds.d_textures; v.perlins = (const DPerlin*)ds.d_perlins;
     v.images = (const DImage*)ds.d_images;
     v.n_prims = (uint32_t)prims.size(); v.n_media = (uint32_t)media.size();
+    v.active_media = (const uint32_t*)ds.d_active_media; v.n_active_media = (uint32_t)active_media.size();
     v.camera = fs.hdr.camera;
     std::memcpy(v.background, fs.hdr.background, sizeof(v.background));
     RT_CUDA(cudaEventRecord(e1, st));
@@ -154,7 +167,9 @@ __global__ void k_first_hit(SceneView sv, const float* rays, int n, float t_min,
     if (i >= n) return;
     const float* q = rays + 7 * (size_t)i;
     Ray r; r.o = make_float3(q[0], q[1], q[2]); r.d = make_float3(q[3], q[4], q[5]); r.tm = q[6];
-    const Closest c = closest_hit<false>(sv, r, t_min, nullptr, xi ? xi + i : nullptr, nullptr);
+    Closest c;
+    if (xi) { const float x = xi[i]; c = closest_hit<false>(sv, r, t_min, true, [x](uint32_t) { return x; }, nullptr); }
+    else c = closest_hit<false>(sv, r, t_min, false, [](uint32_t) { return 1.0f; }, nullptr);
     int32_t id = -1;
     if (c.prim >= 0) id = (int32_t)sv.prim_leaf_id[c.prim];
     else if (c.prim <= -2) id = (int32_t)sv.media[-2 - c.prim].leaf_id;

@@ -58,6 +58,7 @@ struct SceneView {
     const uint32_t* prim_leaf_id;  // DFS leaf id per primitive (tie-breaks, first-hit output)
     const DPrim* bprims;           // medium boundary primitives
     const DMedium* media;
+    const uint32_t* active_media;  // indices of the media that can report a hit at all (see commit_impl)
     const rt_flat_tri_attr* tri_attrs;
     const rt_flat_xop* xops;
     const rt_flat_chain* chains;
@@ -66,7 +67,7 @@ struct SceneView {
     const DPerlin* perlins;
     const DImage* images;
     const BNode* nodes;            // nodes[0] = root (n_prims >= 1)
-    uint32_t n_prims, n_media, n_nodes, pad;
+    uint32_t n_prims, n_media, n_nodes, n_active_media;
     rt_flat_camera camera;
     float background[3];
     float pad2;
@@ -79,6 +80,7 @@ struct DeviceScene {
     void* d_prims = nullptr; void* d_prim_leaf_id = nullptr; void* d_bprims = nullptr; void* d_media = nullptr;
     void* d_tri_attrs = nullptr; void* d_xops = nullptr; void* d_chains = nullptr; void* d_materials = nullptr;
     void* d_textures = nullptr; void* d_perlins = nullptr; void* d_images = nullptr; void* d_nodes = nullptr;
+    void* d_active_media = nullptr;
     cudaArray_t* image_arrays = nullptr;
     cudaTextureObject_t* image_objs = nullptr;
     uint32_t n_images = 0;

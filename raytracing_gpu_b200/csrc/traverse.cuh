@@ -79,18 +79,19 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
 // Media are evaluated after the surfaces with t_max = closest surface.  In the reference a medium sees only
 // the objects listed BEFORE it (hittable_list.h:29-35); because constant_medium clips its exit to t_max before
 // sampling (constant_medium.h:44) the result is the same except where the sampled distance lands within one
-// rounding step of a later surface.  xi: scripted draw (first-hit queries) or NULL for Philox.
-template <bool COUNT>
-__device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& ray, float t_min, const RngKey* g, const float* scripted_xi,
+// rounding step of a later surface.  xi_of(m): the uniform draw of medium m (scripted for first-hit queries,
+// Philox in the renderer); only evaluated when the ray really crosses the boundary.
+template <bool COUNT, class XiOf>
+__device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& ray, float t_min, bool with_media, XiOf&& xi_of,
                                                TraversalCounters* cnt) {
     Closest best; best.t = INFINITY; best.prim = -1;
     closest_surface<COUNT>(sv, ray, t_min, best, cnt);
-    if (g || scripted_xi) {
-        for (uint32_t m = 0; m < sv.n_media; m++) {
+    if (with_media) {
+        for (uint32_t a = 0; a < sv.n_active_media; a++) {
+            const uint32_t m = sv.active_media[a];
             const DMedium med = sv.media[m];
-            auto xi = [&]() { return scripted_xi ? *scripted_xi : draw4(*g, RT_STREAM_MEDIUM, m).x; };
             float t;
-            if (medium_t(sv, med, ray, t_min, best.t, xi, t)) { best.t = t; best.prim = -2 - (int)m; }
+            if (medium_t(sv, med, ray, t_min, best.t, [&]() { return xi_of(m); }, t)) { best.t = t; best.prim = -2 - (int)m; }
         }
     }
     return best;
