@@ -1,17 +1,22 @@
 // wavefront.cu — streaming wavefront path tracer (replaces the render megakernel + color_f, render.h:55-113).
 //
-// A fixed pool of path slots lives in HBM as SoA.  One iteration =
-//   extend    persistent warps pull 32 queued paths at a time, traverse the LBVH + media, write the hit, and append
-//             the path to the shade queue of its material class (warp-ballot aggregated appends)
-//   shade     one launch over all material queues; each warp works inside ONE queue, so a warp shades one
-//             material class; terminated paths add thr*L to the accumulation buffer (float atomics) and are
-//             REGENERATED in place: the slot fetches the next (pixel, sample) from a global cursor (one atomic
-//             per warp) and starts a new camera path; survivors and regenerated paths are appended to the next
-//             extend queue (warp-ballot compaction)
-//   turnover  a one-thread kernel that rolls queue counters over and publishes the live-path count
-// (generate, the camera ray-generation kernel, fills the pool once at the start of a frame.)
-// The pool stays full until the samples run out, so kernels stay large; no host synchronisation inside the loop
-// (the host polls a pinned counter a few iterations behind).
+// Path state lives in HBM as SoA in TWO pools (ping-pong).  Every iteration reads pool `cur` and writes the
+// survivors COMPACTED into pool `next`, so every global access of the hot kernels is a coalesced stream —
+// there is no slot indirection and no index queue:
+//
+//   pool layout      bounced paths occupy positions [0, n_bounce), freshly generated camera paths occupy
+//                    [capacity - n_fresh, capacity).  Keeping the two apart means extend warps are either all
+//                    camera rays of neighbouring pixels (coherent) or all bounced rays.
+//   extend           persistent warps claim 32 consecutive paths, traverse the BVH + media (render.h:63) and
+//                    write an 8-byte hit record + a 1-byte material class at the same position.
+//   shade            persistent blocks claim tiles of 256 consecutive paths, sort the tile by material class in
+//                    shared memory (so a warp shades one class), evaluate hit attributes / textures / scatter,
+//                    add thr*L of terminated paths to the accumulation buffer (float atomics), REGENERATE
+//                    terminated paths from the global sample cursor, and append survivors / new camera paths to
+//                    pool `next`.  All allocation is block-aggregated: three atomics per 256 paths.
+//   turnover         one thread: roll the counters and publish the live-path count to pinned host memory.
+// The pools stay full until the samples run out; the host never synchronises inside a frame (it polls the
+// live count a few iterations behind).
 #include "device_scene.h"
 #include "device_scene.cuh"
 #include "shade.cuh"
@@ -23,28 +28,27 @@
 
 namespace rtb {
 
-constexpr int NQ = 6;                 // shade queues: 0 = miss, 1 + rt_material_type
+constexpr int NQ = 6;                 // material classes: 0 = miss, 1 + rt_material_type
 constexpr int Q_MISS = 0;
 constexpr int POLL_DEPTH = 4;         // host runs this many iterations ahead of the counter it polls
 constexpr int POLL_SLOTS = 8;
 
-struct Counters {
-    uint32_t n_extend[2];
-    uint32_t n_shade[NQ];
-    uint32_t n_new;
-    uint32_t cur_extend, cur_shade, cur_new;
-    unsigned long long next_sample;   // global sample cursor (sample-major: g = sample * npix + pixel)
-    unsigned long long total_rays, started, nodes, prim_tests;
+// every hot counter on its own 128-byte line (its own L2 slice): same-line atomics serialise
+struct __align__(128) Counters {
+    uint32_t n_bounce[2];             uint32_t pad0[30];
+    uint32_t n_fresh[2];              uint32_t pad1[30];
+    uint32_t cur_extend;              uint32_t pad2[31];
+    uint32_t cur_shade;               uint32_t pad3[31];
+    unsigned long long next_sample;   unsigned long long pad4[15];   // global sample cursor (sample-major: g = sample * npix + pixel)
+    unsigned long long total_rays, nodes, prim_tests;
 };
 
 struct PoolView {
-    float4* ray_o;     // origin.xyz, time
-    float4* ray_d;     // direction.xyz, hit t (written by extend)
-    int* hit_prim;     // Closest::prim
-    float4* thr;       // throughput rgb
-    uint2* pid;        // pixel, sample | bounce << 24
-    uint32_t* q_extend[2];
-    uint32_t* q_shade; // NQ * capacity
+    float4* ray_o[2];    // origin.xyz, time
+    float4* ray_d[2];    // direction.xyz, bits: sample | bounce << 24
+    float4* thr[2];      // throughput rgb, bits: pixel
+    uint2* hit;          // written by extend: bits of t, Closest::prim
+    uint8_t* hit_class;  // written by extend: material class of the hit
     Counters* c;
     uint32_t capacity;
 };
@@ -56,14 +60,14 @@ struct RenderPool {
     Counters* h_counters = nullptr;   // pinned copy for stats
     cudaEvent_t poll_ev[POLL_SLOTS]{};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    int grid_extend = 0, grid_shade = 0, grid_gen = 0;
-    std::vector<cudaEvent_t> timer_ev;   // RT_RENDER_TIMERS: 4 events per iteration, reused across frames
+    int grid_extend = 0, grid_shade = 0;
+    std::vector<cudaEvent_t> timer_ev;   // RT_RENDER_TIMERS: 3 events per iteration, reused across frames
 };
 
 void render_pool_destroy(RenderPool* p) {
     if (!p) return;
-    cudaFree(p->v.ray_o); cudaFree(p->v.ray_d); cudaFree(p->v.hit_prim); cudaFree(p->v.thr); cudaFree(p->v.pid);
-    cudaFree(p->v.q_extend[0]); cudaFree(p->v.q_extend[1]); cudaFree(p->v.q_shade); cudaFree(p->v.c);
+    for (int b = 0; b < 2; b++) { cudaFree(p->v.ray_o[b]); cudaFree(p->v.ray_d[b]); cudaFree(p->v.thr[b]); }
+    cudaFree(p->v.hit); cudaFree(p->v.hit_class); cudaFree(p->v.c);
     if (p->h_live) cudaFreeHost(p->h_live);
     if (p->h_counters) cudaFreeHost(p->h_counters);
     for (auto& e : p->poll_ev) if (e) cudaEventDestroy(e);
@@ -84,20 +88,16 @@ struct FrameParams {
     float* accum;                       // width*height*3 sums
 };
 
-constexpr int BLOCK = 128;
+constexpr int EXTEND_BLOCK = 128;
+constexpr int SHADE_BLOCK = 256;
+constexpr int SHADE_WARPS = SHADE_BLOCK / 32;
 
-// warp-aggregated append: all lanes call; lanes with `pred` get consecutive slots in the queue
-__device__ __forceinline__ void warp_append(bool pred, uint32_t* queue, uint32_t* counter, uint32_t value) {
-    const uint32_t mask = __ballot_sync(0xffffffffu, pred);
-    if (!mask) return;
-    const uint32_t lane = threadIdx.x & 31;
-    uint32_t base = 0;
-    if (lane == (uint32_t)(__ffs(mask) - 1)) base = atomicAdd(counter, (uint32_t)__popc(mask));
-    base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
-    if (pred) queue[base + __popc(mask & ((1u << lane) - 1u))] = value;
+// work index -> pool position: bounced paths first, fresh camera paths at the top end of the pool
+__device__ __forceinline__ uint32_t pos_of(uint32_t idx, uint32_t n_bounce, uint32_t n, uint32_t capacity) {
+    return idx < n_bounce ? idx : capacity - n + idx;
 }
 
-// persistent work fetch: a warp claims 32 consecutive queue entries
+// persistent work fetch: a warp claims 32 consecutive paths
 __device__ __forceinline__ uint32_t warp_claim(uint32_t* cursor) {
     uint32_t base = 0;
     if ((threadIdx.x & 31) == 0) base = atomicAdd(cursor, 32u);
@@ -116,78 +116,57 @@ __device__ __forceinline__ void split_sample_index(const FrameParams& fp, unsign
     sample = fp.sample_first + (uint32_t)q;
 }
 
-// camera ray generation for one slot (render.h:105-108)
-__device__ __forceinline__ void start_path(const SceneView& sv, const PoolView& pv, const FrameParams& fp, uint32_t slot, unsigned long long g) {
+// camera ray generation into pool `buf` at `pos` (render.h:105-108)
+__device__ __forceinline__ void start_path(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int buf, uint32_t pos, unsigned long long g) {
     uint32_t pixel, sample;
     split_sample_index(fp, g, pixel, sample);
     const RngKey key{pixel, sample, 0u, fp.seed};
     const uint32_t py = pixel / fp.width, px = pixel - py * fp.width;
     const Ray r = camera_ray(sv.camera, key, (int)px, (int)py, (int)fp.width, (int)fp.height);
-    pv.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.tm);
-    pv.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
-    pv.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-    pv.pid[slot] = make_uint2(pixel, sample);   // bounce 0
+    pv.ray_o[buf][pos] = make_float4(r.o.x, r.o.y, r.o.z, r.tm);
+    pv.ray_d[buf][pos] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(sample));   // bounce 0
+    pv.thr[buf][pos] = make_float4(1.f, 1.f, 1.f, __uint_as_float(pixel));
 }
 
-// lanes with `want` claim consecutive global sample indices: one 64-bit atomic per warp
-__device__ __forceinline__ unsigned long long claim_samples(bool want, unsigned long long* cursor) {
-    const uint32_t mask = __ballot_sync(0xffffffffu, want);
-    if (!mask) return ~0ull;
-    const uint32_t lane = threadIdx.x & 31;
-    const int leader = __ffs(mask) - 1;
-    unsigned long long g0 = 0;
-    if ((int)lane == leader) g0 = atomicAdd(cursor, (unsigned long long)__popc(mask));
-    g0 = __shfl_sync(0xffffffffu, g0, leader);
-    return g0 + __popc(mask & ((1u << lane) - 1u));
-}
-
-// ---- generate -------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_generate(SceneView sv, PoolView pv, FrameParams fp, int next) {
-    // start of a frame: every slot [0, capacity) is free
-    const uint32_t n = pv.capacity;
-    const uint32_t lane = threadIdx.x & 31;
-    for (;;) {
-        const uint32_t base = warp_claim(&pv.c->cur_new);
-        if (base >= n) break;
-        const uint32_t slot = base + lane;
-        const bool have_slot = slot < n;
-        const unsigned long long g = claim_samples(have_slot, &pv.c->next_sample);
-        const bool live = have_slot && g < fp.total_samples;
-        if (live) start_path(sv, pv, fp, slot, g);
-        warp_append(live, pv.q_extend[next], &pv.c->n_extend[next], slot);
-    }
+// ---- generate: fills the fresh region of pool 0 at the start of a frame ---------------------------
+__global__ void __launch_bounds__(256) k_generate(SceneView sv, PoolView pv, FrameParams fp, uint32_t n_fresh) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { pv.c->n_fresh[0] = n_fresh; pv.c->next_sample = n_fresh; }
+    if (i < n_fresh) start_path(sv, pv, fp, 0, pv.capacity - n_fresh + i, i);
 }
 
 // ---- extend ---------------------------------------------------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(BLOCK) k_extend(SceneView sv, PoolView pv, FrameParams fp, int cur) {
-    const uint32_t n = pv.c->n_extend[cur];
+__global__ void __launch_bounds__(EXTEND_BLOCK) k_extend(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+    const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
     const uint32_t lane = threadIdx.x & 31;
+    const float4* __restrict__ ray_o = pv.ray_o[cur];
+    const float4* __restrict__ ray_d = pv.ray_d[cur];
+    const float4* thr = pv.thr[cur];
     TraversalCounters tc{0, 0};
     for (;;) {
         const uint32_t base = warp_claim(&pv.c->cur_extend);
         if (base >= n) break;
         const uint32_t idx = base + lane;
-        const bool valid = idx < n;
-        uint32_t slot = 0;
-        int q = -1;
-        if (valid) {
-            slot = pv.q_extend[cur][idx];
-            const float4 o = pv.ray_o[slot], d = pv.ray_d[slot];
-            const uint2 id = pv.pid[slot];
+        if (idx < n) {
+            const uint32_t pos = pos_of(idx, n_b, n, pv.capacity);
+            const float4 o = ray_o[pos], d = ray_d[pos];
             Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
-            const RngKey key{id.x, id.y & 0xffffffu, id.y >> 24, fp.seed};
-            const Closest c = closest_hit<COUNT>(sv, r, 0.001f, &key, nullptr, &tc);      // render.h:63
-            pv.ray_d[slot].w = c.t;
-            pv.hit_prim[slot] = c.prim;
-            if (c.prim == -1) q = Q_MISS;
-            else {
+            // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched
+            // when a ray really crosses a medium boundary
+            const Closest c = closest_hit<COUNT>(sv, r, 0.001f, true, [&](uint32_t m) {                      // render.h:63
+                const uint32_t sb = __float_as_uint(d.w);
+                const RngKey key{__float_as_uint(thr[pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
+                return draw4(key, RT_STREAM_MEDIUM, m).x;
+            }, &tc);
+            int q = Q_MISS;
+            if (c.prim != -1) {
                 const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
                 q = 1 + (int)sv.materials[mat].type;
             }
+            pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
+            pv.hit_class[pos] = (uint8_t)q;
         }
-        #pragma unroll
-        for (int k = 0; k < NQ; k++) warp_append(q == k, pv.q_shade + (size_t)k * pv.capacity, &pv.c->n_shade[k], slot);
     }
     if (COUNT) {
         atomicAdd(&pv.c->nodes, (unsigned long long)tc.nodes);
@@ -202,55 +181,91 @@ __device__ __forceinline__ void accumulate(float* accum, uint32_t pixel, float3 
     if (c.z != 0.f) atomicAdd(&accum[3 * (size_t)pixel + 2], c.z);
 }
 
-__global__ void __launch_bounds__(BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int next) {
-    // chunk table: queue k owns warp-chunks [first[k], first[k+1])
-    uint32_t first[NQ + 1];
-    first[0] = 0;
-    #pragma unroll
-    for (int k = 0; k < NQ; k++) first[k + 1] = first[k] + (pv.c->n_shade[k] + 31u) / 32u;
-    const uint32_t lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+    constexpr int NC = NQ + 1;                       // + "no path" (tile tail)
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_cnt[64];                   // [class][warp] counts -> exclusive offsets (NC * SHADE_WARPS = 56 used)
+    __shared__ uint16_t s_perm[SHADE_BLOCK];         // sorted rank -> tile-local index | class << 12
+    __shared__ uint32_t s_wcont[SHADE_WARPS], s_wterm[SHADE_WARPS];
+    __shared__ uint32_t s_base_b, s_base_f, s_nregen;
+    __shared__ unsigned long long s_g0;
+    static_assert(NC * SHADE_WARPS <= 64, "class table must fit one warp scan of two cells per lane");
+
+    const int next = cur ^ 1;
+    const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0;
     for (;;) {
-        uint32_t chunk = 0;
-        if (lane == 0) chunk = atomicAdd(&pv.c->cur_shade, 1u);
-        chunk = __shfl_sync(0xffffffffu, chunk, 0);
-        if (chunk >= first[NQ]) break;
-        int k = 0;
-        #pragma unroll
-        for (int t = 1; t < NQ; t++) if (chunk >= first[t]) k = t;
-        const uint32_t idx = (chunk - first[k]) * 32u + lane;
-        const bool valid = idx < pv.c->n_shade[k];
+        if (threadIdx.x == 0) s_tile = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= n) break;
+
+        // -- sort the tile by material class (counting sort: ballots -> [class][warp] table -> one warp scan)
+        {
+            const uint32_t idx = tile + threadIdx.x;
+            int cls = NQ;
+            if (idx < n) cls = pv.hit_class[pos_of(idx, n_b, n, pv.capacity)];
+            uint32_t rank = 0;
+            #pragma unroll
+            for (int k = 0; k < NC; k++) {
+                const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
+                if (cls == k) rank = __popc(m & lt);
+                if ((int)lane == k) s_cnt[k * SHADE_WARPS + warp] = __popc(m);
+            }
+            __syncthreads();
+            if (warp == 0) {
+                const uint32_t v0 = s_cnt[2 * lane], v1 = s_cnt[2 * lane + 1];
+                uint32_t x = v0 + v1;
+                #pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)lane >= o) x += y; }
+                const uint32_t ex = x - (v0 + v1);
+                s_cnt[2 * lane] = ex;
+                s_cnt[2 * lane + 1] = ex + v0;
+            }
+            __syncthreads();
+            s_perm[s_cnt[cls * SHADE_WARPS + warp] + rank] = (uint16_t)(threadIdx.x | (cls << 12));
+            __syncthreads();
+        }
+        const uint32_t e = s_perm[threadIdx.x];
+        const int k = (int)(e >> 12);
+
+        // -- shade one path
         bool continues = false, terminated = false;
-        uint32_t slot = 0;
-        if (valid) {
-            slot = pv.q_shade[(size_t)k * pv.capacity + idx];
-            const float4 th = pv.thr[slot];
-            const uint2 id = pv.pid[slot];
+        float4 new_o, new_d, new_thr;
+        if (k < NQ) {
+            const uint32_t pos = pos_of(tile + (e & 0xfffu), n_b, n, pv.capacity);
+            const float4 th = pv.thr[cur][pos];
+            const float4 d = pv.ray_d[cur][pos];
+            const uint32_t pixel = __float_as_uint(th.w), sb = __float_as_uint(d.w);
+            const uint32_t sample = sb & 0xffffffu, bounce = sb >> 24;
             float3 thr = make_float3(th.x, th.y, th.z);
-            const uint32_t bounce = id.y >> 24;
             terminated = true;
             if (k == Q_MISS) {
-                accumulate(fp.accum, id.x, thr * f3(sv.background[0], sv.background[1], sv.background[2]));   // render.h:64
+                accumulate(fp.accum, pixel, thr * f3(sv.background[0], sv.background[1], sv.background[2]));   // render.h:64
             } else {
-                const float4 o = pv.ray_o[slot], d = pv.ray_d[slot];
+                const float4 o = pv.ray_o[cur][pos];
+                const uint2 h = pv.hit[pos];
                 Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
-                const int prim = pv.hit_prim[slot];
+                const int prim = (int)h.y;
+                const float t = __uint_as_float(h.x);
                 HitAttr rec;
                 uint32_t mat;
-                if (prim >= 0) { const DPrim p = sv.prims[prim]; prim_attr(sv, p, r, d.w, rec); mat = p.material; }
-                else { const DMedium m = sv.media[-2 - prim]; medium_attr(sv, m, r, d.w, rec); mat = m.material; }
+                if (prim >= 0) { const DPrim p = sv.prims[prim]; prim_attr(sv, p, r, t, rec); mat = p.material; }
+                else { const DMedium m = sv.media[-2 - prim]; medium_attr(sv, m, r, t, rec); mat = m.material; }
                 const rt_flat_material m = sv.materials[mat];
                 if (m.type == RT_MAT_DIFFUSE_LIGHT) {
-                    accumulate(fp.accum, id.x, thr * texture_value(sv, m.texture, rec.u, rec.v, rec.p));           // render.h:68, :75
+                    accumulate(fp.accum, pixel, thr * texture_value(sv, m.texture, rec.u, rec.v, rec.p));           // render.h:68, :75
                 } else {
-                    const RngKey key{id.x, id.y & 0xffffffu, bounce, fp.seed};
+                    const RngKey key{pixel, sample, bounce, fp.seed};
                     float3 attenuation;
                     Ray scattered;
                     if (material_scatter(sv, m, r, rec, key, attenuation, scattered) && bounce + 1 < fp.max_depth) {   // render.h:70-73, :80
                         thr = thr * attenuation;
-                        pv.ray_o[slot] = make_float4(scattered.o.x, scattered.o.y, scattered.o.z, scattered.tm);
-                        pv.ray_d[slot] = make_float4(scattered.d.x, scattered.d.y, scattered.d.z, 0.f);
-                        pv.thr[slot] = make_float4(thr.x, thr.y, thr.z, 0.f);
-                        pv.pid[slot] = make_uint2(id.x, (id.y & 0xffffffu) | ((bounce + 1) << 24));
+                        new_o = make_float4(scattered.o.x, scattered.o.y, scattered.o.z, scattered.tm);
+                        new_d = make_float4(scattered.d.x, scattered.d.y, scattered.d.z, __uint_as_float(sample | ((bounce + 1) << 24)));
+                        new_thr = make_float4(thr.x, thr.y, thr.z, th.w);
                         continues = true;
                         terminated = false;
                     }
@@ -258,22 +273,52 @@ __global__ void __launch_bounds__(BLOCK) k_shade(SceneView sv, PoolView pv, Fram
                 }
             }
         }
-        // regeneration: a terminated path's slot immediately starts the next camera sample (if any are left)
-        const unsigned long long g = claim_samples(terminated, &pv.c->next_sample);
-        if (terminated && g < fp.total_samples) { start_path(sv, pv, fp, slot, g); continues = true; }
-        warp_append(continues, pv.q_extend[next], &pv.c->n_extend[next], slot);
+
+        // -- block-aggregated allocation in pool `next`: survivors at the bottom, regenerated camera paths
+        //    (the next samples of the global cursor) at the top
+        const uint32_t mc = __ballot_sync(0xffffffffu, continues), mt = __ballot_sync(0xffffffffu, terminated);
+        if (lane == 0) { s_wcont[warp] = __popc(mc); s_wterm[warp] = __popc(mt); }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t nc = 0, nt = 0;
+            #pragma unroll
+            for (int w = 0; w < SHADE_WARPS; w++) {
+                const uint32_t a = s_wcont[w], b = s_wterm[w];
+                s_wcont[w] = nc; s_wterm[w] = nt;           // exclusive prefixes
+                nc += a; nt += b;
+            }
+            s_base_b = nc ? atomicAdd(&pv.c->n_bounce[next], nc) : 0u;
+            uint32_t n_regen = 0;
+            unsigned long long g0 = 0;
+            if (nt) {
+                g0 = atomicAdd(&pv.c->next_sample, (unsigned long long)nt);
+                if (g0 < fp.total_samples) n_regen = (uint32_t)min((unsigned long long)nt, fp.total_samples - g0);
+            }
+            s_base_f = n_regen ? atomicAdd(&pv.c->n_fresh[next], n_regen) : 0u;
+            s_nregen = n_regen;
+            s_g0 = g0;
+        }
+        __syncthreads();
+        if (continues) {
+            const uint32_t dst = s_base_b + s_wcont[warp] + __popc(mc & lt);
+            pv.ray_o[next][dst] = new_o;
+            pv.ray_d[next][dst] = new_d;
+            pv.thr[next][dst] = new_thr;
+        }
+        if (terminated) {
+            const uint32_t r = s_wterm[warp] + __popc(mt & lt);
+            if (r < s_nregen) start_path(sv, pv, fp, next, pv.capacity - (s_base_f + s_nregen) + r, s_g0 + r);
+        }
     }
 }
 
 // ---- turnover -------------------------------------------------------------------------------------
-__global__ void k_turnover(PoolView pv, int cur, int next, uint32_t* live_out) {
+__global__ void k_turnover(PoolView pv, int cur, uint32_t* live_out) {
     Counters* c = pv.c;
-    c->total_rays += c->n_extend[cur];
-    c->n_extend[cur] = 0;
-    for (int k = 0; k < NQ; k++) c->n_shade[k] = 0;
-    c->n_new = 0;
-    c->cur_extend = 0; c->cur_shade = 0; c->cur_new = 0;
-    *live_out = c->n_extend[next];
+    c->total_rays += c->n_bounce[cur] + c->n_fresh[cur];
+    c->n_bounce[cur] = 0; c->n_fresh[cur] = 0;
+    c->cur_extend = 0; c->cur_shade = 0;
+    *live_out = c->n_bounce[cur ^ 1] + c->n_fresh[cur ^ 1];
 }
 
 __global__ void k_scale(const float* sums, float* out, size_t n, float scale) {
@@ -285,14 +330,14 @@ int pool_create(DeviceScene& ds, uint32_t capacity) {
     RenderPool* p = new RenderPool;
     p->device = ds.device;
     p->v.capacity = capacity;
-    RT_CUDA(cudaMalloc(&p->v.ray_o, sizeof(float4) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.ray_d, sizeof(float4) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.hit_prim, sizeof(int) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.thr, sizeof(float4) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.pid, sizeof(uint2) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.q_extend[0], sizeof(uint32_t) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.q_extend[1], sizeof(uint32_t) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.q_shade, sizeof(uint32_t) * (size_t)capacity * NQ));
+    ds.pool = p;   // owned from here on: a failed allocation below is cleaned up with the scene
+    for (int b = 0; b < 2; b++) {
+        RT_CUDA(cudaMalloc(&p->v.ray_o[b], sizeof(float4) * capacity));
+        RT_CUDA(cudaMalloc(&p->v.ray_d[b], sizeof(float4) * capacity));
+        RT_CUDA(cudaMalloc(&p->v.thr[b], sizeof(float4) * capacity));
+    }
+    RT_CUDA(cudaMalloc(&p->v.hit, sizeof(uint2) * capacity));
+    RT_CUDA(cudaMalloc(&p->v.hit_class, sizeof(uint8_t) * capacity));
     RT_CUDA(cudaMalloc(&p->v.c, sizeof(Counters)));
     RT_CUDA(cudaHostAlloc(&p->h_live, sizeof(uint32_t) * POLL_SLOTS, cudaHostAllocMapped));
     RT_CUDA(cudaHostAlloc(&p->h_counters, sizeof(Counters), cudaHostAllocDefault));
@@ -301,13 +346,10 @@ int pool_create(DeviceScene& ds, uint32_t capacity) {
     int sms = 0;
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
     int occ = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend<false>, BLOCK, 0));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend<false>, EXTEND_BLOCK, 0));
     p->grid_extend = sms * std::max(occ, 1);
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, BLOCK, 0));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, SHADE_BLOCK, 0));
     p->grid_shade = sms * std::max(occ, 1);
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_generate, BLOCK, 0));
-    p->grid_gen = sms * std::max(occ, 1);
-    ds.pool = p;
     return RT_OK;
 }
 
@@ -341,28 +383,28 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
     FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, 0u, total, npix, magic, d_accum};
     uint64_t launches = 0, iterations = 0;
+    float ms_gen = 0.f;
     RT_CUDA(cudaMemsetAsync(P.v.c, 0, sizeof(Counters), stream));
     RT_CUDA(cudaEventRecord(P.ev_begin, stream));
     if (total > 0) {
-        // frame start: fill the pool
-        k_generate<<<P.grid_gen, BLOCK, 0, stream>>>(ds.view, P.v, fp, 0);
+        // frame start: the first min(capacity, total) samples fill pool 0
+        const uint32_t n0 = (uint32_t)std::min<unsigned long long>(capacity, total);
+        k_generate<<<(n0 + 255) / 256, 256, 0, stream>>>(ds.view, P.v, fp, n0);
+        launches += 1;
         uint32_t* d_live = nullptr;
         RT_CUDA(cudaHostGetDevicePointer(&d_live, P.h_live, 0));
-        k_turnover<<<1, 1, 0, stream>>>(P.v, 1, 0, d_live);     // clears cursors; "cur" = the empty queue 1
-        launches += 2;
         bool done = false;
         // hard bound: every iteration with live paths retires >= 1 segment of a path of <= max_depth segments
         const uint64_t max_iterations = (total / capacity + 2) * (uint64_t)st.max_depth + POLL_DEPTH + 64;
         for (uint64_t it = 0; !done; it++) {
-            const int cur = (int)(it & 1), next = cur ^ 1;
+            const int cur = (int)(it & 1);
             if (tick() < 0) return RT_ERR_CUDA;
-            if (count) k_extend<true><<<P.grid_extend, BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
-            else k_extend<false><<<P.grid_extend, BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            if (count) k_extend<true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            else k_extend<false><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
             if (tick() < 0) return RT_ERR_CUDA;
-            k_shade<<<P.grid_shade, BLOCK, 0, stream>>>(ds.view, P.v, fp, next);
+            k_shade<<<P.grid_shade, SHADE_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
             if (tick() < 0) return RT_ERR_CUDA;
-            if (tick() < 0) return RT_ERR_CUDA;
-            k_turnover<<<1, 1, 0, stream>>>(P.v, cur, next, d_live + (it % POLL_SLOTS));
+            k_turnover<<<1, 1, 0, stream>>>(P.v, cur, d_live + (it % POLL_SLOTS));
             RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
             launches += 3;
             iterations++;
@@ -374,6 +416,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
             if (it > max_iterations) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
         }
     }
+    if (tick() < 0) return RT_ERR_CUDA;
     RT_CUDA(cudaEventRecord(P.ev_end, stream));
     RT_CUDA(cudaMemcpyAsync(P.h_counters, P.v.c, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
     RT_CUDA(cudaStreamSynchronize(stream));
@@ -387,17 +430,17 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         stats->nodes_visited = P.h_counters->nodes;
         stats->prim_tests = P.h_counters->prim_tests;
         cudaEventElapsedTime(&stats->ms_total, P.ev_begin, P.ev_end);
-        if (timers) {   // per-kernel device time, summed over the iterations of this frame
-            double ext = 0, shd = 0, gen = 0, fin = 0;
-            for (size_t k = 0; k + 3 < n_timer; k += 4) {
+        if (timers) {   // per-kernel device time, summed over the iterations of this frame: 3 events per iteration + 1
+            double ext = 0, shd = 0, fin = 0;
+            for (size_t k = 0; k + 3 < n_timer; k += 3) {
                 float a = 0, b = 0, c = 0;
                 cudaEventElapsedTime(&a, P.timer_ev[k], P.timer_ev[k + 1]);
                 cudaEventElapsedTime(&b, P.timer_ev[k + 1], P.timer_ev[k + 2]);
                 cudaEventElapsedTime(&c, P.timer_ev[k + 2], P.timer_ev[k + 3]);
-                ext += a; shd += b; gen += c;
-                if (k + 4 < n_timer) { float d = 0; cudaEventElapsedTime(&d, P.timer_ev[k + 3], P.timer_ev[k + 4]); fin += d; }
+                ext += a; shd += b; fin += c;
             }
-            stats->ms_extend = (float)ext; stats->ms_shade = (float)shd; stats->ms_generate = (float)gen; stats->ms_finish = (float)fin;
+            if (n_timer) cudaEventElapsedTime(&ms_gen, P.ev_begin, P.timer_ev[0]);
+            stats->ms_extend = (float)ext; stats->ms_shade = (float)shd; stats->ms_generate = ms_gen; stats->ms_finish = (float)fin;
         }
     }
     return RT_OK;
