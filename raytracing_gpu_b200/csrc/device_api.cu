@@ -164,12 +164,16 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
 
 __global__ void k_first_hit(SceneView sv, const float* rays, int n, float t_min, const float* xi, int32_t* out_id, float* out_t) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float* q = rays + 7 * (size_t)i;
-    Ray r; r.o = make_float3(q[0], q[1], q[2]); r.d = make_float3(q[3], q[4], q[5]); r.tm = q[6];
-    Closest c;
-    if (xi) { const float x = xi[i]; c = closest_hit<false>(sv, r, t_min, true, [x](uint32_t) { return x; }, nullptr); }
-    else c = closest_hit<false>(sv, r, t_min, false, [](uint32_t) { return 1.0f; }, nullptr);
+    const bool active = i < n;                     // closest_hit is warp-collective: idle lanes take part in its votes
+    Ray r; r.o = make_float3(0.f, 0.f, 0.f); r.d = make_float3(0.f, 0.f, 1.f); r.tm = 0.f;
+    float x = 1.0f;
+    if (active) {
+        const float* q = rays + 7 * (size_t)i;
+        r.o = make_float3(q[0], q[1], q[2]); r.d = make_float3(q[3], q[4], q[5]); r.tm = q[6];
+        if (xi) x = xi[i];
+    }
+    const Closest c = closest_hit<false>(sv, r, t_min, xi != nullptr, [x](uint32_t) { return x; }, nullptr, active);
+    if (!active) return;
     int32_t id = -1;
     if (c.prim >= 0) id = (int32_t)sv.prim_leaf_id[c.prim];
     else if (c.prim <= -2) id = (int32_t)sv.media[-2 - c.prim].leaf_id;

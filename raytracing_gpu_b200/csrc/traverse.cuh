@@ -5,6 +5,7 @@
 
 #include "intersect.cuh"
 #include "rng.cuh"
+#include <climits>
 
 namespace rtb {
 
@@ -23,9 +24,13 @@ __device__ __forceinline__ void consider(const SceneView& sv, int prim, float t,
     if (t < best.t || best.prim < 0 || sv.prim_leaf_id[prim] > sv.prim_leaf_id[best.prim]) { best.t = t; best.prim = prim; }
 }
 
+// Experiment record (profiles/r01_v4_parked_leaf_experiment.md): parking a reached leaf and testing parked leaves
+// warp-wide only when a lane reaches a second one was measured 7 % SLOWER than this fused node-or-leaf loop
+// (extra votes per step, +4 % nodes and +10 % primitive tests from the later-shrinking t_max).
+#define RT_NODE_DONE INT_MIN
+
 template <bool COUNT>
-__device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& ray, float t_min, Closest& best, TraversalCounters* cnt) {
-    if (sv.n_prims == 0) return;
+__device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& ray, float t_min, Closest& best, TraversalCounters* cnt, bool active) {
     // slab set-up: t = plane * inv - o * inv as one FMA; zero direction components are nudged so inv stays finite
     const float tiny = 1e-20f;
     const float ix = 1.0f / (fabsf(ray.d.x) < tiny ? copysignf(tiny, ray.d.x) : ray.d.x);
@@ -39,8 +44,8 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
 
     int stack[RT_STACK];
     int sp = 0;
-    int node = 0;
-    for (;;) {
+    int node = (active && sv.n_prims) ? 0 : RT_NODE_DONE;
+    while (node != RT_NODE_DONE) {
         if (node >= 0) {
             const BNode* np = sv.nodes + node;
             const float4 n0 = __ldg(&np->n0), n1 = __ldg(&np->n1), n2 = __ldg(&np->n2);
@@ -71,8 +76,7 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
             float t;
             if (prim_t_local(p, chain ? cached : ray, t_min, best.t, t)) consider(sv, prim, t, best);
         }
-        if (sp == 0) break;
-        node = stack[--sp];
+        node = sp ? stack[--sp] : RT_NODE_DONE;
     }
 }
 
@@ -81,12 +85,13 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
 // sampling (constant_medium.h:44) the result is the same except where the sampled distance lands within one
 // rounding step of a later surface.  xi_of(m): the uniform draw of medium m (scripted for first-hit queries,
 // Philox in the renderer); only evaluated when the ray really crosses the boundary.
+// Lanes without a ray pass active = false (callers keep whole warps converged around the query).
 template <bool COUNT, class XiOf>
 __device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& ray, float t_min, bool with_media, XiOf&& xi_of,
-                                               TraversalCounters* cnt) {
+                                               TraversalCounters* cnt, bool active = true) {
     Closest best; best.t = INFINITY; best.prim = -1;
-    closest_surface<COUNT>(sv, ray, t_min, best, cnt);
-    if (with_media) {
+    closest_surface<COUNT>(sv, ray, t_min, best, cnt, active);
+    if (with_media && active) {
         for (uint32_t a = 0; a < sv.n_active_media; a++) {
             const uint32_t m = sv.active_media[a];
             const DMedium med = sv.media[m];

@@ -148,17 +148,18 @@ __global__ void __launch_bounds__(EXTEND_BLOCK) k_extend(SceneView sv, PoolView 
         const uint32_t base = warp_claim(&pv.c->cur_extend);
         if (base >= n) break;
         const uint32_t idx = base + lane;
-        if (idx < n) {
-            const uint32_t pos = pos_of(idx, n_b, n, pv.capacity);
-            const float4 o = ray_o[pos], d = ray_d[pos];
-            Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
-            // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched
-            // when a ray really crosses a medium boundary
-            const Closest c = closest_hit<COUNT>(sv, r, 0.001f, true, [&](uint32_t m) {                      // render.h:63
-                const uint32_t sb = __float_as_uint(d.w);
-                const RngKey key{__float_as_uint(thr[pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
-                return draw4(key, RT_STREAM_MEDIUM, m).x;
-            }, &tc);
+        const bool active = idx < n;                // closest_hit is warp-collective
+        const uint32_t pos = pos_of(active ? idx : base, n_b, n, pv.capacity);
+        const float4 o = ray_o[pos], d = ray_d[pos];
+        Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
+        // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched
+        // when a ray really crosses a medium boundary
+        const Closest c = closest_hit<COUNT>(sv, r, 0.001f, true, [&](uint32_t m) {                      // render.h:63
+            const uint32_t sb = __float_as_uint(d.w);
+            const RngKey key{__float_as_uint(thr[pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
+            return draw4(key, RT_STREAM_MEDIUM, m).x;
+        }, &tc, active);
+        if (active) {
             int q = Q_MISS;
             if (c.prim != -1) {
                 const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
