@@ -24,12 +24,17 @@ __device__ __forceinline__ void consider(const SceneView& sv, int prim, float t,
     if (t < best.t || best.prim < 0 || sv.prim_leaf_id[prim] > sv.prim_leaf_id[best.prim]) { best.t = t; best.prim = prim; }
 }
 
-// Experiment record (profiles/r01_v4_parked_leaf_experiment.md): parking a reached leaf and testing parked leaves
-// warp-wide only when a lane reaches a second one was measured 7 % SLOWER than this fused node-or-leaf loop
-// (extra votes per step, +4 % nodes and +10 % primitive tests from the later-shrinking t_max).
+// Two loop shapes (profiles/r01_v4_experiments.md):
+//   PARKED = false  fused node-or-leaf step per iteration.  ncu: 35 % of its issue slots go to the leaf code at
+//                   3.2 active lanes of 32, because almost every iteration SOME lane is at a leaf.
+//   PARKED = true   a lane that reaches a leaf parks it (one register) and keeps walking; the warp enters the leaf
+//                   code only when some lane reaches a second leaf or nobody has nodes left, then every parked leaf
+//                   is tested together.  Parking only delays the shrinking of t_max and consider() is
+//                   order-independent, so the closest hit is the same; measured 2.7 % faster on the final scene.
+//                   WARP-COLLECTIVE (votes): every lane of the warp must call, idle lanes with active = false.
 #define RT_NODE_DONE INT_MIN
 
-template <bool COUNT>
+template <bool COUNT, bool PARKED = false>
 __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& ray, float t_min, Closest& best, TraversalCounters* cnt, bool active) {
     // slab set-up: t = plane * inv - o * inv as one FMA; zero direction components are nudged so inv stays finite
     const float tiny = 1e-20f;
@@ -45,6 +50,50 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     int stack[RT_STACK];
     int sp = 0;
     int node = (active && sv.n_prims) ? 0 : RT_NODE_DONE;
+    if constexpr (PARKED) {
+        int parked = RT_NODE_DONE;
+        auto pop = [&]() { return sp ? stack[--sp] : RT_NODE_DONE; };
+        for (;;) {
+            if (node >= 0) {
+                const BNode* np = sv.nodes + node;
+                const float4 n0 = __ldg(&np->n0), n1 = __ldg(&np->n1), n2 = __ldg(&np->n2);
+                const int2 ch = __ldg(reinterpret_cast<const int2*>(&np->child0));
+                if (COUNT) cnt->nodes++;
+                const float c0lox = fmaf(n0.x, ix, -ox), c0hix = fmaf(n0.y, ix, -ox), c0loy = fmaf(n0.z, iy, -oy), c0hiy = fmaf(n0.w, iy, -oy);
+                const float c1lox = fmaf(n1.x, ix, -ox), c1hix = fmaf(n1.y, ix, -ox), c1loy = fmaf(n1.z, iy, -oy), c1hiy = fmaf(n1.w, iy, -oy);
+                const float c0loz = fmaf(n2.x, iz, -oz), c0hiz = fmaf(n2.y, iz, -oz), c1loz = fmaf(n2.z, iz, -oz), c1hiz = fmaf(n2.w, iz, -oz);
+                const float t0n = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
+                const float t0f = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
+                const float t1n = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
+                const float t1f = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), best.t));
+                const bool h0 = t0n <= t0f, h1 = t1n <= t1f;
+                if (h0 && h1) {
+                    const bool swap = t1n < t0n;
+                    stack[sp++] = swap ? ch.x : ch.y;
+                    node = swap ? ch.y : ch.x;
+                } else if (h0) node = ch.x;
+                else if (h1) node = ch.y;
+                else node = pop();
+                if (node < 0 && node != RT_NODE_DONE && parked == RT_NODE_DONE) { parked = node; node = pop(); }
+            }
+            const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
+            if (__any_sync(0xffffffffu, blocked) || !__any_sync(0xffffffffu, node >= 0)) {
+                if (parked != RT_NODE_DONE) {
+                    const int prim = ~parked;
+                    parked = RT_NODE_DONE;
+                    const DPrim p = sv.prims[prim];
+                    const uint32_t chain = prim_chain(p);
+                    if (chain != cached_chain) { cached = to_object_space(sv, chain, ray); cached_chain = chain; }
+                    if (COUNT) cnt->prim_tests++;
+                    float t;
+                    if (prim_t_local(p, chain ? cached : ray, t_min, best.t, t)) consider(sv, prim, t, best);
+                }
+                if (blocked) { parked = node; node = pop(); }
+                if (!__any_sync(0xffffffffu, node != RT_NODE_DONE || parked != RT_NODE_DONE)) break;
+            }
+        }
+        return;
+    }
     while (node != RT_NODE_DONE) {
         if (node >= 0) {
             const BNode* np = sv.nodes + node;
@@ -86,11 +135,11 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
 // rounding step of a later surface.  xi_of(m): the uniform draw of medium m (scripted for first-hit queries,
 // Philox in the renderer); only evaluated when the ray really crosses the boundary.
 // Lanes without a ray pass active = false (callers keep whole warps converged around the query).
-template <bool COUNT, class XiOf>
+template <bool COUNT, bool PARKED = false, class XiOf>
 __device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& ray, float t_min, bool with_media, XiOf&& xi_of,
                                                TraversalCounters* cnt, bool active = true) {
     Closest best; best.t = INFINITY; best.prim = -1;
-    closest_surface<COUNT>(sv, ray, t_min, best, cnt, active);
+    closest_surface<COUNT, PARKED>(sv, ray, t_min, best, cnt, active);
     if (with_media && active) {
         for (uint32_t a = 0; a < sv.n_active_media; a++) {
             const uint32_t m = sv.active_media[a];

@@ -8,7 +8,8 @@
 //                    [capacity - n_fresh, capacity).  Keeping the two apart means extend warps are either all
 //                    camera rays of neighbouring pixels (coherent) or all bounced rays.
 //   extend           persistent warps claim 32 consecutive paths, traverse the BVH + media (render.h:63) and
-//                    write an 8-byte hit record + a 1-byte material class at the same position.
+//                    write an 8-byte hit record + a 1-byte material class at the same position.  Leaf tests are
+//                    parked and run warp-wide (traverse.cuh).
 //   shade            persistent blocks claim tiles of 256 consecutive paths, sort the tile by material class in
 //                    shared memory (so a warp shades one class), evaluate hit attributes / textures / scatter,
 //                    add thr*L of terminated paths to the accumulation buffer (float atomics), REGENERATE
@@ -60,7 +61,7 @@ struct RenderPool {
     Counters* h_counters = nullptr;   // pinned copy for stats
     cudaEvent_t poll_ev[POLL_SLOTS]{};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    int grid_extend = 0, grid_shade = 0;
+    int grid_extend = 0, grid_shade = 0, shade_block = 256;
     std::vector<cudaEvent_t> timer_ev;   // RT_RENDER_TIMERS: 3 events per iteration, reused across frames
 };
 
@@ -89,8 +90,6 @@ struct FrameParams {
 };
 
 constexpr int EXTEND_BLOCK = 128;
-constexpr int SHADE_BLOCK = 256;
-constexpr int SHADE_WARPS = SHADE_BLOCK / 32;
 
 // work index -> pool position: bounced paths first, fresh camera paths at the top end of the pool
 __device__ __forceinline__ uint32_t pos_of(uint32_t idx, uint32_t n_bounce, uint32_t n, uint32_t capacity) {
@@ -116,12 +115,35 @@ __device__ __forceinline__ void split_sample_index(const FrameParams& fp, unsign
     sample = fp.sample_first + (uint32_t)q;
 }
 
+// Film order: consecutive sample-cursor values walk the frame in 8x4-pixel tiles (one warp = one tile) inside bands
+// of four rows, so the camera rays of a warp form a compact beam and the paths that descend from them stay
+// neighbours in the pools.  Every pixel still receives every sample index exactly once; the Philox key is the
+// (pixel, sample) pair, so the image does not depend on this order.
+__device__ __forceinline__ void film_xy(const FrameParams& fp, uint32_t i, uint32_t& px, uint32_t& py) {
+    const uint32_t band = i / (4u * fp.width);                 // bands of 4 rows (the last one may be shorter)
+    const uint32_t y0 = 4u * band;
+    const uint32_t hb = min(4u, fp.height - y0);
+    const uint32_t r = i - band * 4u * fp.width;               // index inside the band
+    const uint32_t full = fp.width >> 3;                       // whole 8-wide tiles
+    const uint32_t tile_px = 8u * hb;
+    if (r < full * tile_px) {
+        const uint32_t t = r / tile_px, w = r - t * tile_px;
+        px = 8u * t + (w & 7u);
+        py = y0 + (w >> 3);
+    } else {                                                    // the narrow last tile of the band
+        const uint32_t j = r - full * tile_px, wr = fp.width & 7u;
+        px = 8u * full + j % wr;
+        py = y0 + j / wr;
+    }
+}
+
 // camera ray generation into pool `buf` at `pos` (render.h:105-108)
 __device__ __forceinline__ void start_path(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int buf, uint32_t pos, unsigned long long g) {
-    uint32_t pixel, sample;
-    split_sample_index(fp, g, pixel, sample);
+    uint32_t index, sample, px, py;
+    split_sample_index(fp, g, index, sample);
+    if (fp.pad & 1u) { py = index / fp.width; px = index - py * fp.width; } else film_xy(fp, index, px, py);
+    const uint32_t pixel = py * fp.width + px;
     const RngKey key{pixel, sample, 0u, fp.seed};
-    const uint32_t py = pixel / fp.width, px = pixel - py * fp.width;
     const Ray r = camera_ray(sv.camera, key, (int)px, (int)py, (int)fp.width, (int)fp.height);
     pv.ray_o[buf][pos] = make_float4(r.o.x, r.o.y, r.o.z, r.tm);
     pv.ray_d[buf][pos] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(sample));   // bounce 0
@@ -136,7 +158,7 @@ __global__ void __launch_bounds__(256) k_generate(SceneView sv, PoolView pv, Fra
 }
 
 // ---- extend ---------------------------------------------------------------------------------------
-template <bool COUNT>
+template <bool COUNT, bool PARKED = false>
 __global__ void __launch_bounds__(EXTEND_BLOCK) k_extend(SceneView sv, PoolView pv, FrameParams fp, int cur) {
     const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
     const uint32_t lane = threadIdx.x & 31;
@@ -154,7 +176,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK) k_extend(SceneView sv, PoolView 
         Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
         // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched
         // when a ray really crosses a medium boundary
-        const Closest c = closest_hit<COUNT>(sv, r, 0.001f, true, [&](uint32_t m) {                      // render.h:63
+        const Closest c = closest_hit<COUNT, PARKED>(sv, r, 0.001f, true, [&](uint32_t m) {                      // render.h:63
             const uint32_t sb = __float_as_uint(d.w);
             const RngKey key{__float_as_uint(thr[pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
             return draw4(key, RT_STREAM_MEDIUM, m).x;
@@ -182,10 +204,12 @@ __device__ __forceinline__ void accumulate(float* accum, uint32_t pixel, float3 
     if (c.z != 0.f) atomicAdd(&accum[3 * (size_t)pixel + 2], c.z);
 }
 
+template <int SHADE_BLOCK>
 __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+    constexpr int SHADE_WARPS = SHADE_BLOCK / 32;
     constexpr int NC = NQ + 1;                       // + "no path" (tile tail)
-    __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_cnt[64];                   // [class][warp] counts -> exclusive offsets (NC * SHADE_WARPS = 56 used)
+    __shared__ uint32_t s_tile[2];                   // this tile / the next one (claimed while this one is shaded)
+    __shared__ uint32_t s_cnt[64];                   // [class][warp] counts -> exclusive offsets
     __shared__ uint16_t s_perm[SHADE_BLOCK];         // sorted rank -> tile-local index | class << 12
     __shared__ uint32_t s_wcont[SHADE_WARPS], s_wterm[SHADE_WARPS];
     __shared__ uint32_t s_base_b, s_base_f, s_nregen;
@@ -197,10 +221,10 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0;
-    for (;;) {
-        if (threadIdx.x == 0) s_tile = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
-        __syncthreads();
-        const uint32_t tile = s_tile;
+    if (threadIdx.x == 0) s_tile[0] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
+    __syncthreads();
+    for (int it = 0;; it ^= 1) {
+        const uint32_t tile = s_tile[it];
         if (tile >= n) break;
 
         // -- sort the tile by material class (counting sort: ballots -> [class][warp] table -> one warp scan)
@@ -275,8 +299,8 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
             }
         }
 
-        // -- block-aggregated allocation in pool `next`: survivors at the bottom, regenerated camera paths
-        //    (the next samples of the global cursor) at the top
+        // -- block-aggregated allocation in pool `next`: survivors at the bottom (tile order kept), regenerated
+        //    camera paths (the next samples of the global cursor) at the top; the next tile is claimed here too
         const uint32_t mc = __ballot_sync(0xffffffffu, continues), mt = __ballot_sync(0xffffffffu, terminated);
         if (lane == 0) { s_wcont[warp] = __popc(mc); s_wterm[warp] = __popc(mt); }
         __syncthreads();
@@ -298,6 +322,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
             s_base_f = n_regen ? atomicAdd(&pv.c->n_fresh[next], n_regen) : 0u;
             s_nregen = n_regen;
             s_g0 = g0;
+            s_tile[it ^ 1] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
         }
         __syncthreads();
         if (continues) {
@@ -347,9 +372,11 @@ int pool_create(DeviceScene& ds, uint32_t capacity) {
     int sms = 0;
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
     int occ = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend<false>, EXTEND_BLOCK, 0));
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend<false, true>, EXTEND_BLOCK, 0));
     p->grid_extend = sms * std::max(occ, 1);
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, SHADE_BLOCK, 0));
+    p->shade_block = (getenv("RT_EXP") && (atoi(getenv("RT_EXP")) & 8)) ? 128 : 256;
+    if (p->shade_block == 128) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<128>, 128, 0));
+    else RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<256>, 256, 0));
     p->grid_shade = sms * std::max(occ, 1);
     return RT_OK;
 }
@@ -365,7 +392,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     RT_CUDA(cudaSetDevice(ds.device));
     const unsigned long long npix = (unsigned long long)st.width * st.height;
     const unsigned long long total = npix * s_count;
-    uint32_t capacity = st.pool_paths ? st.pool_paths : (1u << 21);
+    uint32_t capacity = st.pool_paths ? st.pool_paths : (1u << 22);
     capacity = (uint32_t)std::min<unsigned long long>(capacity, std::max<unsigned long long>(total, 32ull));
     capacity = (capacity + 31u) & ~31u;
     if (ds.pool && ds.pool->v.capacity != capacity) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
@@ -382,7 +409,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     };
 
     const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
-    FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, 0u, total, npix, magic, d_accum};
+    FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, (uint32_t)(getenv("RT_EXP") ? atoi(getenv("RT_EXP")) : 0), total, npix, magic, d_accum};
     uint64_t launches = 0, iterations = 0;
     float ms_gen = 0.f;
     RT_CUDA(cudaMemsetAsync(P.v.c, 0, sizeof(Counters), stream));
@@ -400,10 +427,12 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         for (uint64_t it = 0; !done; it++) {
             const int cur = (int)(it & 1);
             if (tick() < 0) return RT_ERR_CUDA;
-            if (count) k_extend<true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
-            else k_extend<false><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            else if (fp.pad & 4u) k_extend<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);   // RT_EXP=4: fused loop
+            else k_extend<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
             if (tick() < 0) return RT_ERR_CUDA;
-            k_shade<<<P.grid_shade, SHADE_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, stream>>>(ds.view, P.v, fp, cur);
+            else k_shade<256><<<P.grid_shade, 256, 0, stream>>>(ds.view, P.v, fp, cur);
             if (tick() < 0) return RT_ERR_CUDA;
             k_turnover<<<1, 1, 0, stream>>>(P.v, cur, d_live + (it % POLL_SLOTS));
             RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
