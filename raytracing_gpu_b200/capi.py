@@ -86,6 +86,12 @@ def lib():
         "rt_render_device": (i32, [vp, C.POINTER(RenderSettings), vp, vp, C.POINTER(RenderStats)]),
         "rt_quantize_frame": (i32, [vp, i32, i32, vp]),
         "rt_catalog_scene": (i32, [vp, C.c_char_p, C.POINTER(CatalogParams), C.POINTER(C.c_float)]),
+        # include/rt_obj.h
+        "rt_obj_load": (i32, [C.c_char_p, C.POINTER(vp)]), "rt_obj_parse": (i32, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(vp)]),
+        "rt_obj_free": (None, [vp]), "rt_obj_num_vertices": (C.c_uint32, [vp]), "rt_obj_num_triangles": (C.c_uint32, [vp]),
+        "rt_obj_vertices": (vp, [vp]), "rt_obj_uvs": (vp, [vp]), "rt_obj_normals": (vp, [vp]), "rt_obj_indices": (vp, [vp]),
+        "rt_obj_normals_generated": (i32, [vp]), "rt_obj_diffuse_map": (C.c_char_p, [vp]),
+        "rt_obj_add_to_scene": (i32, [vp, vp, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)      # AttributeError here means the .so does not export a declared symbol
@@ -264,3 +270,65 @@ class Scene:
         stats = RenderStats()
         _check(lib().rt_render_device(self._h, C.byref(st), C.c_void_p(d_accum_ptr), C.c_void_p(stream or 0), C.byref(stats)))
         return stats
+
+
+class ObjMesh:
+    """include/rt_obj.h: a Wavefront OBJ parsed by the library's own loader (replaces the reference's assimp path)."""
+
+    def __init__(self, path=None, text=None, mtl_text=None):
+        self._h = C.c_void_p()
+        if path is not None:
+            _check(lib().rt_obj_load(os.fsencode(path), C.byref(self._h)))
+        else:
+            t = text.encode() if isinstance(text, str) else bytes(text)
+            m = None if mtl_text is None else (mtl_text.encode() if isinstance(mtl_text, str) else bytes(mtl_text))
+            _check(lib().rt_obj_parse(t, len(t), m, len(m) if m is not None else 0, C.byref(self._h)))
+
+    def __del__(self):
+        try:
+            if self._h:
+                lib().rt_obj_free(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def _array(self, fn, count, dtype):
+        ptr = fn(self._h)
+        if not ptr or count == 0:
+            return np.zeros(0, dtype)
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float if dtype == np.float32 else C.c_uint32)), shape=(count,)).copy()
+
+    @property
+    def n_vertices(self):
+        return int(lib().rt_obj_num_vertices(self._h))
+
+    @property
+    def n_triangles(self):
+        return int(lib().rt_obj_num_triangles(self._h))
+
+    @property
+    def vertices(self):
+        return self._array(lib().rt_obj_vertices, 3 * self.n_vertices, np.float32).reshape(-1, 3)
+
+    @property
+    def uvs(self):
+        return self._array(lib().rt_obj_uvs, 2 * self.n_vertices, np.float32).reshape(-1, 2)
+
+    @property
+    def normals(self):
+        return self._array(lib().rt_obj_normals, 3 * self.n_vertices, np.float32).reshape(-1, 3)
+
+    @property
+    def indices(self):
+        return self._array(lib().rt_obj_indices, 3 * self.n_triangles, np.uint32).reshape(-1, 3)
+
+    @property
+    def normals_generated(self):
+        return bool(lib().rt_obj_normals_generated(self._h))
+
+    @property
+    def diffuse_map(self):
+        return lib().rt_obj_diffuse_map(self._h).decode()
+
+    def add_to_scene(self, scene, mat):
+        return _check(lib().rt_obj_add_to_scene(scene._h, self._h, int(mat)))

@@ -14,9 +14,15 @@ ROOT = helpers.ROOT
 
 
 def declared_functions():
-    src = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(rt_[a-z_0-9]+)\s*\(", src)))
+    names = set()
+    for hdr in ("rt_b200.h", "rt_catalog.h", "rt_obj.h", "rt_output.h"):      # every C-ABI header of include/
+        path = os.path.join(ROOT, "include", hdr)
+        if not os.path.exists(path):
+            continue
+        src = open(path).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names |= set(re.findall(r"\b(rt_[a-z_0-9]+)\s*\(", src))
+    return sorted(names)
 
 
 def test_library_exports_every_declared_symbol():
