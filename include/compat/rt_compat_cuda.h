@@ -5,6 +5,7 @@
 #include <functional>
 #include <iostream>
 #include "../rt_compat.h"
+#include "../rt_obj.h"
 
 // device allocations of the scene files are small host arrays here (hittable** lists, curandState, ...)
 static inline cudaError_t rtc_host_alloc(void** p, size_t n) { *p = calloc(1, n ? n : 1); return cudaSuccess; }
@@ -59,10 +60,25 @@ inline bool read_ppm(const char* path, std::vector<unsigned char>& out, int& w, 
 }
 
 // Mesh loading hook: bool(path, vertices, indices, uvs, texture_paths, normals) — same outputs as the
-// reference's load_model (triangle_mesh.h:129).  The library's own OBJ loader is installed by rt_obj.h.
+// reference's load_model (triangle_mesh.h:129).  When no hook is installed the library's own OBJ loader is used.
 using mesh_loader_fn = std::function<bool(const std::string&, std::vector<float>&, std::vector<unsigned>&, std::vector<float>&,
                                           std::vector<std::string>&, std::vector<float>&)>;
 inline mesh_loader_fn& mesh_loader() { static mesh_loader_fn f; return f; }
+
+// Default mesh loader: the library's own OBJ / MTL reader (include/rt_obj.h) in place of assimp.
+inline bool load_obj_builtin(const std::string& path, std::vector<float>& vertices, std::vector<unsigned>& indices, std::vector<float>& uvs,
+                             std::vector<std::string>& tex_paths, std::vector<float>& norms) {
+    rt_obj* o = nullptr;
+    if (rt_obj_load(path.c_str(), &o) < 0) { std::cerr << "OBJ loader error:\n\t" << rt_last_error() << std::endl; return false; }   // triangle_mesh.h:137-140
+    const uint32_t nv = rt_obj_num_vertices(o), nt = rt_obj_num_triangles(o);
+    vertices.assign(rt_obj_vertices(o), rt_obj_vertices(o) + 3 * (size_t)nv);
+    uvs.assign(rt_obj_uvs(o), rt_obj_uvs(o) + 2 * (size_t)nv);
+    norms.assign(rt_obj_normals(o), rt_obj_normals(o) + 3 * (size_t)nv);
+    indices.assign(rt_obj_indices(o), rt_obj_indices(o) + 3 * (size_t)nt);
+    if (rt_obj_diffuse_map(o)[0]) tex_paths.push_back(rt_obj_diffuse_map(o));
+    rt_obj_free(o);
+    return true;
+}
 } // namespace rtc
 
 // make_image(paths, data, widths, heights, channels) — texture.h:188-203
@@ -105,9 +121,10 @@ inline void create_meshes_d(hittable** hits, unsigned* num_tris, unsigned num_ob
 // create_meshes(objs, hits, num_data, size) — triangle_mesh.h:208-352
 inline void create_meshes(std::vector<std::string> objs, hittable**& hits, thrust::device_ptr<unsigned>& num_data, int& size) {
     if (objs.size() != 1) throw std::runtime_error("rt_compat: create_meshes supports one .obj per call (SURVEY Q11)");
-    if (!rtc::mesh_loader()) throw std::runtime_error("rt_compat: no mesh loader installed (include rt_obj.h)");
     std::vector<float> vertices, uvs, norms; std::vector<unsigned> indices; std::vector<std::string> tex_paths;
-    if (!rtc::mesh_loader()(objs[0], vertices, indices, uvs, tex_paths, norms)) throw std::runtime_error("rt_compat: cannot load " + objs[0]);
+    const bool loaded = rtc::mesh_loader() ? rtc::mesh_loader()(objs[0], vertices, indices, uvs, tex_paths, norms)
+                                           : rtc::load_obj_builtin(objs[0], vertices, indices, uvs, tex_paths, norms);
+    if (!loaded) throw std::runtime_error("rt_compat: cannot load " + objs[0]);
     if (tex_paths.size() != 1) { std::cerr << "Meshes need exactly 1 texture" << std::endl; return; }   // triangle_mesh.h:275-281
     const std::string dir = objs[0].substr(0, objs[0].find_last_of('/') + 1);
     const std::string tex = dir + tex_paths[0];

@@ -3,7 +3,8 @@ daRoyalCacti/Raytracing_GPU.  The product is the C-ABI shared library ``librt_b2
 this package is a thin ctypes binding over it plus helpers for tests and benchmarks.  There is no CPU or
 PyTorch fallback: anything that needs the GPU raises when the library or the device is missing."""
 from .capi import (Scene, RenderSettings, RenderStats, BuildStats, RtError, lib, lib_path, image_height,
-                   quantize_frame, ObjMesh)
+                   quantize_frame, ObjMesh, DrawSettings, average_frames, write_ppm, write_png)
 
 __all__ = ["Scene", "RenderSettings", "RenderStats", "BuildStats", "RtError", "lib", "lib_path", "image_height",
-           "quantize_frame", "ObjMesh"]
+           "quantize_frame", "ObjMesh", "DrawSettings", "average_frames", "write_ppm",
+           "write_png"]

@@ -41,6 +41,12 @@ class CatalogParams(C.Structure):
                 ("n_triangles", C.c_int), ("uvs", C.c_void_p), ("normals", C.c_void_p), ("camera15", C.c_void_p)]
 
 
+class DrawSettings(C.Structure):
+    _fields_ = [("image_width", C.c_uint32), ("image_height", C.c_uint32), ("aspect_ratio", C.c_float),
+                ("samples_per_pixel_per_fb", C.c_uint32), ("no_fb", C.c_uint32), ("max_depth", C.c_uint32),
+                ("seed", C.c_uint32), ("device", C.c_uint32), ("reserved", C.c_uint32 * 8)]
+
+
 RENDER_COUNTERS = 1
 
 _lib = None
@@ -92,6 +98,10 @@ def lib():
         "rt_obj_vertices": (vp, [vp]), "rt_obj_uvs": (vp, [vp]), "rt_obj_normals": (vp, [vp]), "rt_obj_indices": (vp, [vp]),
         "rt_obj_normals_generated": (i32, [vp]), "rt_obj_diffuse_map": (C.c_char_p, [vp]),
         "rt_obj_add_to_scene": (i32, [vp, vp, i32]),
+        # include/rt_output.h
+        "rt_average_frames": (i32, [vp, i32, i32, i32, vp]), "rt_write_ppm": (i32, [C.c_char_p, vp, i32, i32]),
+        "rt_write_png": (i32, [C.c_char_p, vp, i32, i32]),
+        "rt_draw": (i32, [vp, C.POINTER(DrawSettings), C.c_char_p, vp, C.POINTER(C.c_uint32), C.POINTER(RenderStats)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)      # AttributeError here means the .so does not export a declared symbol
@@ -111,12 +121,34 @@ def image_height(width, aspect):
     return lib().rt_image_height(int(width), float(aspect))
 
 
+image_height_of = image_height
+
+
 def quantize_frame(rgb):
     rgb = _f32(rgb)
     h, w, _ = rgb.shape
     out = np.empty((h, w, 3), np.uint8)
     _check(lib().rt_quantize_frame(rgb.ctypes.data, w, h, out.ctypes.data))
     return out
+
+
+def average_frames(frames):
+    """include/rt_output.h: average_images' arithmetic on (n, H, W, 3) uint8 quantised frames."""
+    fr = np.ascontiguousarray(frames, dtype=np.uint8)
+    n, h, w, _ = fr.shape
+    out = np.empty((h, w, 3), np.uint8)
+    _check(lib().rt_average_frames(fr.ctypes.data, n, w, h, out.ctypes.data))
+    return out
+
+
+def write_ppm(path, rgb8):
+    px = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    _check(lib().rt_write_ppm(os.fsencode(path), px.ctypes.data, px.shape[1], px.shape[0]))
+
+
+def write_png(path, rgb8):
+    px = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    _check(lib().rt_write_png(os.fsencode(path), px.ctypes.data, px.shape[1], px.shape[0]))
 
 
 def _check(rc):
@@ -260,6 +292,19 @@ class Scene:
         out = np.empty((height, width, 3), np.float32)
         stats = RenderStats()
         _check(lib().rt_render(self._h, C.byref(st), out.ctypes.data, C.byref(stats)))
+        return out, stats
+
+    def draw(self, image_width, aspect_ratio, samples_per_pixel_per_fb, no_fb, max_depth=50, seed=1984, png_path=None,
+             image_height=0, device=0):
+        """include/rt_output.h rt_draw: the reference's draw() (render.h:118) — batches, 8-bit quantisation, averaging, PNG."""
+        st = DrawSettings(image_width=image_width, image_height=image_height, aspect_ratio=aspect_ratio,
+                          samples_per_pixel_per_fb=samples_per_pixel_per_fb, no_fb=no_fb, max_depth=max_depth, seed=seed, device=device)
+        h = image_height or (image_height_of(image_width, aspect_ratio) if aspect_ratio > 0 and image_width > 0 else 0)
+        out = np.empty((max(h, 1), max(image_width, 1), 3), np.uint8)
+        hh = C.c_uint32()
+        stats = RenderStats()
+        _check(lib().rt_draw(self._h, C.byref(st), os.fsencode(png_path) if png_path else None, out.ctypes.data, C.byref(hh), C.byref(stats)))
+        assert hh.value == h
         return out, stats
 
     def render_device(self, d_accum_ptr, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0,

@@ -1,0 +1,142 @@
+// output.cpp — the reference's image output stage (include/rt_output.h): color.h:19-49, :57-170, render.h:152-168.
+#include "../../include/rt_output.h"
+#include "device_scene.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace rtb;
+
+namespace {
+
+int fail(int code, const std::string& msg) { set_error(msg); return code; }
+
+uint32_t crc_table[256];
+bool crc_ready = false;
+uint32_t crc32_update(uint32_t crc, const uint8_t* p, size_t n) {
+    if (!crc_ready) {
+        for (uint32_t i = 0; i < 256; i++) { uint32_t c = i; for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1; crc_table[i] = c; }
+        crc_ready = true;
+    }
+    for (size_t i = 0; i < n; i++) crc = crc_table[(crc ^ p[i]) & 0xff] ^ (crc >> 8);
+    return crc;
+}
+void put_be32(std::vector<uint8_t>& v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
+void put_chunk(std::vector<uint8_t>& out, const char type[4], const std::vector<uint8_t>& data) {
+    put_be32(out, (uint32_t)data.size());
+    const size_t start = out.size();
+    out.insert(out.end(), type, type + 4);
+    out.insert(out.end(), data.begin(), data.end());
+    put_be32(out, crc32_update(0xffffffffu, out.data() + start, out.size() - start) ^ 0xffffffffu);
+}
+
+} // namespace
+
+extern "C" {
+
+int rt_average_frames(const uint8_t* frames, int n_frames, int width, int height, uint8_t* out) {
+    if (!frames || !out || n_frames <= 0 || width <= 0 || height <= 0) return fail(RT_ERR_INVALID, "average_frames: bad argument");
+    const size_t n = (size_t)width * height * 3;
+    std::vector<float> fb(n, 0.0f);
+    for (int f = 0; f < n_frames; f++) {
+        const uint8_t* src = frames + (size_t)f * n;
+        for (size_t k = 0; k < n; k++) {
+            const int v = src[k];
+            fb[k] += (v * v) / (255.0f * 255.0f);          // color.h:125 (int product, float quotient), :127
+        }
+    }
+    for (size_t k = 0; k < n; k++) {
+        float v = fb[k];
+        v /= n_frames;                                      // color.h:150-152
+        v = std::sqrt(v);                                   // color.h:156-158
+        v = v < 0.0f ? 0.0f : (v > 0.999f ? 0.999f : v);    // color.h:161-163
+        out[k] = (uint8_t)static_cast<int>(256 * v);
+    }
+    return RT_OK;
+}
+
+int rt_write_ppm(const char* path, const uint8_t* rgb8, int width, int height) {
+    if (!path || !rgb8 || width <= 0 || height <= 0) return fail(RT_ERR_INVALID, "write_ppm: bad argument");
+    FILE* f = fopen(path, "w");
+    if (!f) return fail(RT_ERR_INVALID, std::string("write_ppm: cannot open ") + path);
+    fprintf(f, "P3\n%d %d\n255\n", width, height);
+    const size_t npix = (size_t)width * height;
+    for (size_t k = 0; k < npix; k++) fprintf(f, "%d %d %d\n", rgb8[3 * k], rgb8[3 * k + 1], rgb8[3 * k + 2]);
+    fclose(f);
+    return RT_OK;
+}
+
+int rt_write_png(const char* path, const uint8_t* rgb8, int width, int height) {
+    if (!path || !rgb8 || width <= 0 || height <= 0) return fail(RT_ERR_INVALID, "write_png: bad argument");
+    std::vector<uint8_t> out = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    std::vector<uint8_t> ihdr;
+    put_be32(ihdr, (uint32_t)width); put_be32(ihdr, (uint32_t)height);
+    ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);   // 8-bit RGB, no interlace
+    put_chunk(out, "IHDR", ihdr);
+    // raw scanlines (filter byte 0 each) inside a zlib stream of stored deflate blocks
+    const size_t stride = (size_t)width * 3 + 1;
+    std::vector<uint8_t> raw(stride * height);
+    for (int j = 0; j < height; j++) { raw[j * stride] = 0; memcpy(&raw[j * stride + 1], rgb8 + (size_t)j * width * 3, (size_t)width * 3); }
+    std::vector<uint8_t> z = {0x78, 0x01};
+    uint32_t a = 1, b = 0;
+    for (size_t off = 0; off < raw.size() || off == 0; ) {
+        const size_t len = raw.size() - off < 65535 ? raw.size() - off : 65535;
+        const bool last = off + len >= raw.size();
+        z.push_back(last ? 1 : 0);
+        z.push_back(len & 0xff); z.push_back(len >> 8); z.push_back(~len & 0xff); z.push_back((~len >> 8) & 0xff);
+        z.insert(z.end(), raw.begin() + off, raw.begin() + off + len);
+        for (size_t i = 0; i < len; i++) { a = (a + raw[off + i]) % 65521u; b = (b + a) % 65521u; }
+        off += len;
+        if (last) break;
+    }
+    put_be32(z, (b << 16) | a);
+    put_chunk(out, "IDAT", z);
+    put_chunk(out, "IEND", {});
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(RT_ERR_INVALID, std::string("write_png: cannot open ") + path);
+    const size_t w = fwrite(out.data(), 1, out.size(), f);
+    fclose(f);
+    return w == out.size() ? RT_OK : fail(RT_ERR_INVALID, "write_png: short write");
+}
+
+int rt_draw(rt_scene* scene, const rt_draw_settings* st, const char* png_path, uint8_t* out_rgb8, uint32_t* out_height, rt_render_stats* stats) {
+    if (!scene || !st) return fail(RT_ERR_INVALID, "draw: bad argument");
+    const uint32_t width = st->image_width ? st->image_width : 1200u;
+    const uint32_t spp = st->samples_per_pixel_per_fb ? st->samples_per_pixel_per_fb : 100u;
+    const uint32_t no_fb = st->no_fb ? st->no_fb : 10u;
+    uint32_t height = st->image_height;
+    if (!height) {
+        if (!(st->aspect_ratio > 0.0f)) return fail(RT_ERR_INVALID, "draw: image_height or aspect_ratio must be given");
+        const int h = rt_image_height((int)width, st->aspect_ratio);
+        if (h <= 0) return fail(RT_ERR_INVALID, "draw: computed image height is not positive");
+        height = (uint32_t)h;
+    }
+    if (!device_of(scene)) { const int rc = rt_scene_commit(scene, (int)st->device, nullptr); if (rc < 0) return rc; }
+    const size_t n = (size_t)width * height * 3;
+    std::vector<float> fb(n);
+    std::vector<uint8_t> frames(n * no_fb), final_px(n);
+    rt_render_stats total{}, one{};
+    for (uint32_t i = 0; i < no_fb; i++) {                  // render.h:152-162
+        rt_render_settings rs{};
+        rs.width = width; rs.height = height; rs.samples_per_pixel = spp * no_fb; rs.max_depth = st->max_depth ? st->max_depth : 50u;
+        rs.seed = st->seed; rs.sample_first = i * spp; rs.sample_count = spp;
+        const int rc = rt_render(scene, &rs, fb.data(), &one);                 // mean of this batch (render.h:112)
+        if (rc < 0) return rc;
+        total.samples += one.samples; total.rays += one.rays; total.iterations += one.iterations; total.kernel_launches += one.kernel_launches;
+        total.ms_total += one.ms_total;
+        const int qc = rt_quantize_frame(fb.data(), (int)width, (int)height, frames.data() + (size_t)i * n);   // color.h:19-49
+        if (qc < 0) return qc;
+    }
+    int rc = rt_average_frames(frames.data(), (int)no_fb, (int)width, (int)height, final_px.data());           // color.h:57-170
+    if (rc < 0) return rc;
+    if (png_path && (rc = rt_write_png(png_path, final_px.data(), (int)width, (int)height)) < 0) return rc;
+    if (out_rgb8) memcpy(out_rgb8, final_px.data(), n);
+    if (out_height) *out_height = height;
+    if (stats) *stats = total;
+    return RT_OK;
+}
+
+} // extern "C"

@@ -61,6 +61,27 @@ def ref_lib():
     return L
 
 
+def ref_output_pipeline(frames, workdir):
+    """The reference's own write_frame_buffer + average_images (color.h) on (n, H, W, 3) linear float frames, run by
+    oracle/_ref/ref_output_tool in its own process.  Returns (final uint8 image, directory holding the PPMs) or None
+    when the tool was never built."""
+    import subprocess
+    tool = os.path.join(ORACLE_DIR, "_ref", "ref_output_tool")
+    if not os.path.exists(tool):
+        return None
+    frames = np.ascontiguousarray(frames, np.float32)
+    n, h, w, _ = frames.shape
+    din = os.path.join(workdir, "in")
+    os.mkdir(din)
+    raw_in, raw_out = os.path.join(workdir, "frames.f32"), os.path.join(workdir, "out.raw")
+    frames.tofile(raw_in)
+    subprocess.check_call([tool, str(n), str(w), str(h), raw_in, din, raw_out])
+    data = open(raw_out, "rb").read()
+    header, _, body = data.partition(b"\n")
+    assert header.split() == [b"RAW8", str(w).encode(), str(h).encode()]
+    return np.frombuffer(body, np.uint8).reshape(h, w, 3).copy(), din
+
+
 def ref_program(L, handle):
     n = L.ref_program_words(handle)
     prog = np.zeros(n, np.uint32)
