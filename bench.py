@@ -188,6 +188,8 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--pool", type=int, default=0, help="wavefront pool size in paths (0 = library default)")
+    ap.add_argument("--partition", default="sample", choices=["sample", "tile"],
+                    help="multi-GPU split: sample ranges (default) or interleaved film blocks; one NCCL reduce either way")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -234,9 +236,12 @@ def main():
 
     def step(flags=0):
         accum.zero_()
-        first, count = sample_range(total_spp, world, rank)
+        if args.partition == "tile":
+            first, count, ti, tc = 0, total_spp, rank, world
+        else:
+            (first, count), ti, tc = sample_range(total_spp, world, rank), 0, 1
         st = sc.render_device(accum.data_ptr(), width, height, total_spp, max_depth=50, seed=SEED, sample_first=first,
-                              sample_count=count, flags=flags, pool_paths=args.pool, stream=stream)
+                              sample_count=count, flags=flags, pool_paths=args.pool, stream=stream, tile_index=ti, tile_count=tc)
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
         torch.mul(accum, 1.0 / total_spp, out=out)
@@ -319,7 +324,7 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": desc, "width": width, "height": height, "spp_per_gpu": spp, "spp_total": total_spp,
-                           "max_depth": 50, "partition": f"sample-split x{world} + one NCCL reduce" if world > 1 else "single GPU",
+                           "max_depth": 50, "partition": f"{args.partition}-split x{world} + one NCCL reduce" if world > 1 else "single GPU",
                            "l2": "working set (pool + queues) > L2; accumulation buffer re-zeroed each step",
                            "prims": int(build.n_prims), "bvh_nodes": int(build.n_nodes), "bvh_build_ms": float(build.ms_total)},
                 "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays_per_step / (npix * total_spp),

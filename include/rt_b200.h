@@ -119,6 +119,8 @@ enum rt_render_flags {
     RT_RENDER_TIMERS = 2    /* CUDA-event time per kernel class (ms_extend / ms_shade / ms_generate / ms_finish) */
 };
 
+#define RT_TILE_BLOCK_PIXELS 1024u
+
 typedef struct rt_render_settings {  /* replaces render_settings (render.h:21-50) */
     uint32_t width, height;
     uint32_t samples_per_pixel;      /* total over all ranks: samples_per_pixel_per_fb * no_fb */
@@ -128,7 +130,11 @@ typedef struct rt_render_settings {  /* replaces render_settings (render.h:21-50
     uint32_t sample_count;           /* 0 = all */
     uint32_t flags;
     uint32_t pool_paths;             /* wavefront pool size in paths; 0 = default */
-    uint32_t reserved[7];
+    uint32_t tile_index, tile_count; /* tile-split partitioning: with tile_count > 1 this call renders only the film blocks
+                                        b with b % tile_count == tile_index (blocks of RT_TILE_BLOCK_PIXELS consecutive
+                                        pixels in film order = 32 tiles of 8x4); the other pixels of the buffer are left
+                                        untouched, so per-rank buffers still sum with ONE reduce.  0 / 1 = whole frame */
+    uint32_t reserved[5];
 } rt_render_settings;
 
 typedef struct rt_render_stats {

@@ -19,7 +19,7 @@ class RenderSettings(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("samples_per_pixel", C.c_uint32),
                 ("max_depth", C.c_uint32), ("seed", C.c_uint32), ("sample_first", C.c_uint32),
                 ("sample_count", C.c_uint32), ("flags", C.c_uint32), ("pool_paths", C.c_uint32),
-                ("reserved", C.c_uint32 * 7)]
+                ("tile_index", C.c_uint32), ("tile_count", C.c_uint32), ("reserved", C.c_uint32 * 5)]
 
 
 class RenderStats(C.Structure):
@@ -286,9 +286,11 @@ class Scene:
                                   ids.ctypes.data, t.ctypes.data))
         return ids, t
 
-    def render(self, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0, flags=0, pool_paths=0):
+    def render(self, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0, flags=0, pool_paths=0,
+               tile_index=0, tile_count=0):
         st = RenderSettings(width=width, height=height, samples_per_pixel=spp, max_depth=max_depth, seed=seed,
-                            sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths)
+                            sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths,
+                            tile_index=tile_index, tile_count=tile_count)
         out = np.empty((height, width, 3), np.float32)
         stats = RenderStats()
         _check(lib().rt_render(self._h, C.byref(st), out.ctypes.data, C.byref(stats)))
@@ -308,10 +310,11 @@ class Scene:
         return out, stats
 
     def render_device(self, d_accum_ptr, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0,
-                      flags=0, pool_paths=0, stream=None):
+                      flags=0, pool_paths=0, stream=None, tile_index=0, tile_count=0):
         """Accumulate sums into a caller-owned device buffer (e.g. a torch CUDA tensor's data_ptr())."""
         st = RenderSettings(width=width, height=height, samples_per_pixel=spp, max_depth=max_depth, seed=seed,
-                            sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths)
+                            sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths,
+                            tile_index=tile_index, tile_count=tile_count)
         stats = RenderStats()
         _check(lib().rt_render_device(self._h, C.byref(st), C.c_void_p(d_accum_ptr), C.c_void_p(stream or 0), C.byref(stats)))
         return stats

@@ -85,8 +85,9 @@ struct FrameParams {
     uint32_t sample_first;
     uint32_t pad;
     unsigned long long total_samples;   // samples this call renders = npix * sample_count
-    unsigned long long npix, npix_magic; // frame size and ceil(2^64 / npix)
+    unsigned long long npix, npix_magic; // film indices this call covers (the frame, or this tile-split share) and ceil(2^64 / npix)
     float* accum;                       // width*height*3 sums
+    uint32_t tile_index, tile_count;    // tile-split: film blocks b with b % tile_count == tile_index (tile_count <= 1: all)
 };
 
 constexpr int EXTEND_BLOCK = 128;
@@ -141,6 +142,10 @@ __device__ __forceinline__ void film_xy(const FrameParams& fp, uint32_t i, uint3
 __device__ __forceinline__ void start_path(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int buf, uint32_t pos, unsigned long long g) {
     uint32_t index, sample, px, py;
     split_sample_index(fp, g, index, sample);
+    if (fp.tile_count > 1u) {   // local film index -> global: the k-th owned block is global block k * tile_count + tile_index
+        const uint32_t k = index / RT_TILE_BLOCK_PIXELS;
+        index = (k * fp.tile_count + fp.tile_index) * RT_TILE_BLOCK_PIXELS + (index - k * RT_TILE_BLOCK_PIXELS);
+    }
     if (fp.pad & 1u) { py = index / fp.width; px = index - py * fp.width; } else film_xy(fp, index, px, py);
     const uint32_t pixel = py * fp.width + px;
     const RngKey key{pixel, sample, 0u, fp.seed};
@@ -390,7 +395,17 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     const uint32_t s_count = st.sample_count ? st.sample_count : st.samples_per_pixel - std::min(st.samples_per_pixel, s_first);
     if ((unsigned long long)s_first + s_count > 0xffffffull) { set_error("render: sample index exceeds 2^24"); return RT_ERR_INVALID; }
     RT_CUDA(cudaSetDevice(ds.device));
-    const unsigned long long npix = (unsigned long long)st.width * st.height;
+    const unsigned long long frame_pix = (unsigned long long)st.width * st.height;
+    if (frame_pix >= (1ull << 32)) { set_error("render: more than 2^32 pixels"); return RT_ERR_INVALID; }
+    unsigned long long npix = frame_pix;
+    const uint32_t tile_count = st.tile_count > 1 ? st.tile_count : 1u;
+    if (st.tile_index >= tile_count) { set_error("render: tile_index >= tile_count"); return RT_ERR_INVALID; }
+    if (tile_count > 1) {   // pixels in the film blocks this call owns; only the last block of the frame can be short
+        const unsigned long long nb = (frame_pix + RT_TILE_BLOCK_PIXELS - 1) / RT_TILE_BLOCK_PIXELS;
+        const unsigned long long owned = nb > st.tile_index ? (nb - st.tile_index + tile_count - 1) / tile_count : 0;
+        npix = owned * RT_TILE_BLOCK_PIXELS;
+        if (owned && (owned - 1) * tile_count + st.tile_index == nb - 1) npix -= nb * RT_TILE_BLOCK_PIXELS - frame_pix;
+    }
     const unsigned long long total = npix * s_count;
     uint32_t capacity = st.pool_paths ? st.pool_paths : (1u << 22);
     capacity = (uint32_t)std::min<unsigned long long>(capacity, std::max<unsigned long long>(total, 32ull));
@@ -409,7 +424,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     };
 
     const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
-    FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, (uint32_t)(getenv("RT_EXP") ? atoi(getenv("RT_EXP")) : 0), total, npix, magic, d_accum};
+    FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, (uint32_t)(getenv("RT_EXP") ? atoi(getenv("RT_EXP")) : 0), total, npix, magic, d_accum, st.tile_index, tile_count};
     uint64_t launches = 0, iterations = 0;
     float ms_gen = 0.f;
     RT_CUDA(cudaMemsetAsync(P.v.c, 0, sizeof(Counters), stream));
