@@ -15,6 +15,8 @@ The earth texture is synthetic (reference assets are not redistributed); all oth
              LBVH build) + render + reduce + D2H of the W*H*3 float image, every step
   roofline   dominant kernel (extend): algorithmic 48 B per ray segment / its CUDA-event time vs measured HBM copy
              bandwidth; the binding roofline (FP32 issue) is reported next to it as roofline_fp32
+  reference_cuda
+             the reference's own CUDA build (oracle/_ref/ref_cuda) on the same GPU, bounded sample, N = 1 only
   cpu_baseline / --impl reference
              the reference's own render()/color_f() (oracle/_ref, its sources compiled for the host) on the box's
              host cores, on a bounded sample of the same frame
@@ -159,6 +161,42 @@ def reference_cpu(workload, steps, warmup, budget_s=12.0):
     value = width * height * ns / t / 1e6
     sample = f"{width}x{height} full frame, {ns} of {spp} spp, depth 50, render pass only, {cores} host threads"
     return {"value": value, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": sample}, t * 1e3
+
+
+def reference_cuda(workload, budget_s=20.0):
+    """The reference's own CUDA build on this GPU (oracle/_ref/ref_cuda: its unmodified headers compiled by nvcc for
+    sm_100, harness oracle/ref_cuda_harness.cu) on a bounded sample of the workload: the full-resolution frame at a
+    sample count chosen from a 1-spp calibration launch.  Reported next to the product's number; never on its path."""
+    import tempfile
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_cuda")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/ref_cuda was not built (needs /root/reference at build time)"}
+    scene_name, width, aspect, spp, desc = WORKLOADS[workload]
+    if scene_name == "mesh":
+        return {"unavailable": "the reference's one-thread O(n^2) BVH build cannot take the 1M-triangle stand-in mesh"}
+    with tempfile.TemporaryDirectory() as d:
+        extra = []
+        if scene_name == "final":
+            img = synthetic_earth()
+            path = os.path.join(d, "earth.rgb8")
+            img.tofile(path)
+            extra = [path, str(img.shape[1]), str(img.shape[0])]
+
+        def run(ns, timeout):
+            out = subprocess.run([exe, scene_name, str(width), str(ns), "50"] + extra, capture_output=True, text=True, timeout=timeout)
+            if out.returncode != 0:
+                raise RuntimeError(f"ref_cuda rc={out.returncode}: {out.stderr[-300:]}")
+            return json.loads(out.stdout.strip().splitlines()[-1])
+        try:
+            cal = run(1, 300)
+            ns = int(max(1, min(spp, budget_s * 1e3 / max(cal["ms_render"], 1e-3))))
+            res = cal if ns == 1 else run(ns, 600)
+        except Exception as e:                               # a crash or time-out of the reference is a result, not an error of this bench
+            return {"unavailable": f"reference CUDA build failed here: {e}"[:300]}
+    return {"value": res["msamples_per_s"], "unit": "Msamples/s", "kind": "reference CUDA build (nvcc sm_100, unmodified headers)",
+            "sample": f"{res['width']}x{res['height']} full frame, {res['spp']} of {spp} spp, depth 50, render<<<>>> launch only (CUDA events)",
+            "ms_render": res["ms_render"], "ms_scene_build": res["ms_build"], "ms_render_init": res["ms_render_init"],
+            "nan_pixels": res["nan_pixels"], "image_mean": res["image_mean"]}
 
 
 def print_reference_line(args):
@@ -315,9 +353,11 @@ def main():
                "h2d_bytes_per_step": blob_bytes + image_bytes, "d2h_bytes_per_step": npix * 12,
                "includes": "rt_scene_commit (scene H2D + GPU LBVH build) + render + reduce + image D2H"}
 
-    cb = None
+    cb = rc = None
     if rank == 0 and not args.no_cpu_baseline:
         cb, _ = reference_cpu(args.workload, 1, 1)
+        if world == 1:
+            rc = reference_cuda(args.workload)
 
     if rank == 0:
         line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
@@ -329,7 +369,7 @@ def main():
                            "prims": int(build.n_prims), "bvh_nodes": int(build.n_nodes), "bvh_build_ms": float(build.ms_total)},
                 "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays_per_step / (npix * total_spp),
                 "gpu_launches": launches, "clocks": clk, "roofline": roofline, "roofline_fp32": roofline_fp32, "e2e": e2e,
-                "cpu_baseline": cb}
+                "cpu_baseline": cb, "reference_cuda": rc}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
