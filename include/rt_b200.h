@@ -101,6 +101,11 @@ int rt_image_height(int width, float aspect);
 typedef struct rt_build_stats {
     uint32_t n_prims, n_nodes;
     float ms_upload, ms_morton, ms_sort, ms_hierarchy, ms_refit, ms_collapse, ms_total;
+    uint32_t bvh_depth;      /* PLOC builds: depth of the tree */
+    uint32_t build_rounds;   /* PLOC builds: clustering rounds */
+    float sah_internal;      /* PLOC builds: sum of internal-node surface areas / root area */
+    uint32_t ploc_radius;    /* PLOC builds: neighbour search radius of the tree that was kept */
+    uint32_t reserved[4];
 } rt_build_stats;
 
 /* Flatten (if needed), upload to `device` and build the LBVH there.  Replaces the one-thread device

@@ -12,7 +12,10 @@
 //   emit          64-byte traversal nodes (parent holds both child boxes) + primitives permuted into leaf order
 #include "device_scene.cuh"
 
+#include <algorithm>
 #include <cfloat>
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 namespace rtb {
@@ -350,6 +353,147 @@ __global__ void k_permute_prims(uint32_t n, const uint32_t* sorted_vals, const D
     leaf_ids_out[j] = leaf_ids_in[p];
 }
 
+// ---------------------------------------------------------------------------------------------------
+// PLOC hierarchy (parallel locally-ordered clustering, after Meister & Bittner 2017) over the Morton-sorted
+// primitives: every cluster looks RADIUS neighbours to each side for the partner that minimises the surface area
+// of the merged box; mutual nearest neighbours merge; the survivors are compacted IN ORDER and the loop repeats
+// until one cluster is left.  Bottom-up, so boxes are exact unions (no refit pass) and the tree is SAH-driven
+// rather than dictated by the Morton prefix structure (Karras), which costs ~1.5-2x the node visits on meshes.
+// Internal nodes are numbered from the top: the last merge is node 0 (the root), so the upper levels of the tree
+// sit together at the start of the node array.
+// ---------------------------------------------------------------------------------------------------
+constexpr int PLOC_MAX_RADIUS = 64;
+constexpr uint32_t PLOC_SWEEP_MAX = 131072;                     // scenes up to this many primitives are built with several radii
+constexpr int PLOC_BLOCK = 256;
+constexpr int SCAN_ITEMS = 8;                                   // per thread
+constexpr int SCAN_TILE = PLOC_BLOCK * SCAN_ITEMS;
+
+__device__ __forceinline__ float half_area_union(float4 alo, float4 ahi, float4 blo, float4 bhi) {
+    const float dx = fmaxf(ahi.x, bhi.x) - fminf(alo.x, blo.x), dy = fmaxf(ahi.y, bhi.y) - fminf(alo.y, blo.y), dz = fmaxf(ahi.z, bhi.z) - fminf(alo.z, blo.z);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_ploc_init(int n, const uint32_t* sorted_vals, const float4* prim_lo, const float4* prim_hi, int* cid, float4* lo, float4* hi) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p = sorted_vals[i];
+    cid[i] = ~i;                       // leaf: ~(index in sorted order) = ~(primitive index after the permutation)
+    float4 l = prim_lo[p];
+    l.w = 0.f;                         // .w of lo carries the subtree depth
+    lo[i] = l;
+    hi[i] = prim_hi[p];
+}
+
+__global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_nn(const float4* lo, const float4* hi, int n, int* nn, int radius) {
+    __shared__ float4 slo[PLOC_BLOCK + 2 * PLOC_MAX_RADIUS], shi[PLOC_BLOCK + 2 * PLOC_MAX_RADIUS];
+    const int first = blockIdx.x * PLOC_BLOCK - radius;
+    for (int t = threadIdx.x; t < PLOC_BLOCK + 2 * radius; t += PLOC_BLOCK) {
+        const int j = first + t;
+        if (j >= 0 && j < n) { slo[t] = lo[j]; shi[t] = hi[j]; }
+    }
+    __syncthreads();
+    const int i = blockIdx.x * PLOC_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const int c = threadIdx.x + radius;
+    const float4 mlo = slo[c], mhi = shi[c];
+    float best = INFINITY;
+    int best_j = -1;
+    #pragma unroll 4
+    for (int d = -radius; d <= radius; d++) {      // ascending j and a strict '<': ties go to the lower index
+        const int j = i + d;
+        if (d == 0 || j < 0 || j >= n) continue;
+        const float a = half_area_union(mlo, mhi, slo[c + d], shi[c + d]);
+        if (a < best) { best = a; best_j = j; }
+    }
+    nn[i] = best_j;
+}
+
+// flags of cluster i packed for one scan: low word = stays in the list, high word = creates a node (the lower index
+// of a mutual pair); the other member of the pair is absorbed
+__device__ __forceinline__ unsigned long long ploc_flags(const int* nn, int n, int i) {
+    if (i >= n) return 0ull;
+    const int j = nn[i];
+    const bool mutual = j >= 0 && nn[j] == i;
+    const bool absorbed = mutual && i > j, leader = mutual && i < j;
+    return (absorbed ? 0ull : 1ull) | (leader ? (1ull << 32) : 0ull);
+}
+
+// block-local exclusive scan of the packed flags; block totals go to sums[]
+__global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_scan_block(const int* nn, int n, unsigned long long* local, unsigned long long* sums) {
+    __shared__ unsigned long long warp_tot[PLOC_BLOCK / 32];
+    const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    unsigned long long v[SCAN_ITEMS], run = 0;
+    #pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) { v[k] = run; run += ploc_flags(nn, n, base + k); }
+    unsigned long long x = run;                               // inclusive scan of the per-thread totals
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_tot[warp] = x;
+    __syncthreads();
+    unsigned long long before = 0;
+    for (int w = 0; w < warp; w++) before += warp_tot[w];
+    const unsigned long long excl = before + x - run;
+    #pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) if (base + k < n) local[base + k] = excl + v[k];
+    if (threadIdx.x == PLOC_BLOCK - 1) sums[blockIdx.x] = before + x;
+}
+
+// exclusive scan of the block totals by one block; the grand total lands in sums[nblocks]
+__global__ void __launch_bounds__(1024) k_ploc_scan_sums(unsigned long long* sums, int nblocks) {
+    __shared__ unsigned long long warp_tot[32];
+    __shared__ unsigned long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < nblocks; base += 1024) {
+        const int i = base + threadIdx.x;
+        const unsigned long long v = i < nblocks ? sums[i] : 0ull;
+        unsigned long long x = v;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        unsigned long long before = 0;
+        for (int w = 0; w < warp; w++) before += warp_tot[w];
+        if (i < nblocks) sums[i] = carry + before + x - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += before + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) sums[nblocks] = carry;
+}
+
+// merge mutual pairs, emit their traversal node, compact the survivors in order
+__global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_merge(const int* nn, int n, const unsigned long long* local, const unsigned long long* sums,
+                                                          const int* cid_in, const float4* lo_in, const float4* hi_in, int* cid_out, float4* lo_out,
+                                                          float4* hi_out, BNode* nodes, int next_node /* index of the first node this round creates */, float* area_sum) {
+    const int i = blockIdx.x * PLOC_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const int j = nn[i];
+    const bool mutual = j >= 0 && nn[j] == i;
+    if (mutual && i > j) return;                               // absorbed by its partner
+    const unsigned long long pos = local[i] + sums[i / SCAN_TILE];
+    const uint32_t p = (uint32_t)pos;
+    float4 alo = lo_in[i], ahi = hi_in[i];
+    int id = cid_in[i];
+    if (mutual) {
+        const float4 blo = lo_in[j], bhi = hi_in[j];
+        const int node = next_node - (int)(pos >> 32);         // numbered downwards: the final merge is node 0
+        BNode b;
+        b.n0 = make_float4(alo.x, ahi.x, alo.y, ahi.y);
+        b.n1 = make_float4(blo.x, bhi.x, blo.y, bhi.y);
+        b.n2 = make_float4(alo.z, ahi.z, blo.z, bhi.z);
+        b.child0 = id; b.child1 = cid_in[j]; b.pad0 = b.pad1 = 0;
+        nodes[node] = b;
+        atomicAdd(area_sum, half_area_union(alo, ahi, blo, bhi));          // SAH bookkeeping: sum of internal-node areas
+        alo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), fmaxf(alo.w, blo.w) + 1.f);
+        ahi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+        id = node;
+    }
+    cid_out[p] = id; lo_out[p] = alo; hi_out[p] = ahi;
+}
+
 template <class T> cudaError_t dalloc(T** p, size_t count) { return cudaMalloc((void**)p, (count ? count : 1) * sizeof(T)); }
 
 } // namespace
@@ -395,11 +539,82 @@ int build_lbvh(DeviceScene& ds, const DPrim* d_prims_in, const uint32_t* d_leaf_
         std::swap(kin, kout); std::swap(vin, vout);
     }
     RT_CUDA(cudaEventRecord(ev[2], stream));
-    if (n > 1) k_karras<<<gb, tb, 0, stream>>>(kin, (int)n, left, right, parent_internal, parent_leaf);
-    RT_CUDA(cudaEventRecord(ev[3], stream));
-    k_refit<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, right, parent_internal, parent_leaf, leaf_lo, leaf_hi, node_lo, node_hi, visit);
-    RT_CUDA(cudaEventRecord(ev[4], stream));
-    k_emit_nodes<<<gb, tb, 0, stream>>>((int)n, left, right, leaf_lo, leaf_hi, node_lo, node_hi, nodes);
+    const char* which = getenv("RT_BVH");
+    const bool use_karras = n == 1 || (which && !strcmp(which, "karras"));   // RT_BVH=karras: the Morton-prefix hierarchy (A/B)
+    if (use_karras) {
+        if (n > 1) k_karras<<<gb, tb, 0, stream>>>(kin, (int)n, left, right, parent_internal, parent_leaf);
+        RT_CUDA(cudaEventRecord(ev[3], stream));
+        k_refit<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, right, parent_internal, parent_leaf, leaf_lo, leaf_hi, node_lo, node_hi, visit);
+        RT_CUDA(cudaEventRecord(ev[4], stream));
+        k_emit_nodes<<<gb, tb, 0, stream>>>((int)n, left, right, leaf_lo, leaf_hi, node_lo, node_hi, nodes);
+    } else {
+        // PLOC: cluster lists ping-pong between (cid_a, leaf_*) and (cid_b, node_*); `left`/`right` double as cid arrays,
+        // `parent_internal` as the nearest-neighbour array.  The search radius trades differently per scene (flat rect
+        // soups like a wide window less than triangle meshes do), and a build is ~1 ms per 250 k primitives, so scenes up
+        // to PLOC_SWEEP_MAX primitives are built with several radii and the tree with the smallest summed internal-node
+        // area (the SAH traversal term) is kept; measured node visits per ray follow that sum (profiles/r01_v5_ploc.md).
+        unsigned long long *scan_local = nullptr, *scan_sums = nullptr;
+        float* area_sum = nullptr;
+        BNode* nodes_alt = nullptr;
+        RT_CUDA(dalloc(&area_sum, 1));
+        const int max_sblk = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+        RT_CUDA(dalloc(&scan_local, n)); RT_CUDA(dalloc(&scan_sums, (size_t)max_sblk + 1));
+        RT_CUDA(cudaEventRecord(ev[3], stream));
+        const char* rad = getenv("RT_PLOC_RADIUS");
+        std::vector<int> radii;
+        if (rad) radii.push_back(std::min(PLOC_MAX_RADIUS, std::max(1, atoi(rad))));
+        else if (n <= PLOC_SWEEP_MAX) radii = {4, 8, 16, 32};
+        else radii = {16};
+        if (radii.size() > 1) RT_CUDA(dalloc(&nodes_alt, n_nodes));
+        const int total_internal = (int)n - 1;
+        float best_area = INFINITY;
+        BNode* best_nodes = nullptr;
+        for (const int radius : radii) {
+            BNode* target = best_nodes == nodes ? nodes_alt : nodes;          // never overwrite the best tree so far
+            int *cid_in = left, *cid_out = right, *nn = parent_internal;
+            float4 *lo_in = leaf_lo, *hi_in = leaf_hi, *lo_out = node_lo, *hi_out = node_hi;
+            RT_CUDA(cudaMemsetAsync(area_sum, 0, sizeof(float), stream));
+            k_ploc_init<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, cid_in, lo_in, hi_in);
+            int cur_n = (int)n, created = 0, rounds = 0;
+            while (cur_n > 1) {
+                const int nblk = (cur_n + PLOC_BLOCK - 1) / PLOC_BLOCK, sblk = (cur_n + SCAN_TILE - 1) / SCAN_TILE;
+                k_ploc_nn<<<nblk, PLOC_BLOCK, 0, stream>>>(lo_in, hi_in, cur_n, nn, radius);
+                k_ploc_scan_block<<<sblk, PLOC_BLOCK, 0, stream>>>(nn, cur_n, scan_local, scan_sums);
+                k_ploc_scan_sums<<<1, 1024, 0, stream>>>(scan_sums, sblk);
+                k_ploc_merge<<<nblk, PLOC_BLOCK, 0, stream>>>(nn, cur_n, scan_local, scan_sums, cid_in, lo_in, hi_in, cid_out, lo_out, hi_out, target,
+                                                              total_internal - 1 - created, area_sum);
+                unsigned long long tot = 0;
+                RT_CUDA(cudaMemcpyAsync(&tot, scan_sums + sblk, sizeof(tot), cudaMemcpyDeviceToHost, stream));
+                RT_CUDA(cudaStreamSynchronize(stream));
+                const int survivors = (int)(uint32_t)tot, merges = (int)(tot >> 32);
+                if (merges <= 0 || survivors != cur_n - merges) { set_error("bvh build: PLOC round made no progress (internal error)"); return RT_ERR_STATE; }
+                cur_n = survivors; created += merges; rounds++;
+                std::swap(cid_in, cid_out); std::swap(lo_in, lo_out); std::swap(hi_in, hi_out);
+            }
+            if (created != total_internal) { set_error("bvh build: PLOC node count mismatch (internal error)"); return RT_ERR_STATE; }
+            float4 root_lo, root_hi;
+            float h_area = 0.f;
+            RT_CUDA(cudaMemcpyAsync(&root_lo, lo_in, sizeof(float4), cudaMemcpyDeviceToHost, stream));
+            RT_CUDA(cudaMemcpyAsync(&root_hi, hi_in, sizeof(float4), cudaMemcpyDeviceToHost, stream));
+            RT_CUDA(cudaMemcpyAsync(&h_area, area_sum, sizeof(float), cudaMemcpyDeviceToHost, stream));
+            RT_CUDA(cudaStreamSynchronize(stream));
+            const uint32_t depth = (uint32_t)root_lo.w;
+            if (depth + 2 > RT_STACK_DEPTH) continue;                         // deeper than the traversal stack: not a candidate
+            if (h_area < best_area) {
+                best_area = h_area; best_nodes = target;
+                const float rdx = root_hi.x - root_lo.x, rdy = root_hi.y - root_lo.y, rdz = root_hi.z - root_lo.z;
+                ds.build.bvh_depth = depth;
+                ds.build.sah_internal = h_area / fmaxf(rdx * rdy + rdy * rdz + rdz * rdx, 1e-30f);
+                ds.build.build_rounds = (uint32_t)rounds;
+                ds.build.ploc_radius = (uint32_t)radius;
+            }
+        }
+        cudaFree(scan_local); cudaFree(scan_sums); cudaFree(area_sum);
+        if (!best_nodes) { cudaFree(nodes_alt); set_error("bvh build: tree deeper than the traversal stack; rebuild with RT_BVH=karras"); return RT_ERR_UNSUPPORTED; }
+        if (best_nodes == nodes_alt) std::swap(nodes, nodes_alt);
+        cudaFree(nodes_alt);
+        RT_CUDA(cudaEventRecord(ev[4], stream));
+    }
     k_permute_prims<<<gb, tb, 0, stream>>>(n, vin, d_prims_in, d_leaf_ids_in, prims_out, leaf_ids_out);
     RT_CUDA(cudaEventRecord(ev[5], stream));
     RT_CUDA(cudaGetLastError());

@@ -73,6 +73,8 @@ struct SceneView {
     float pad2;
 };
 
+#define RT_STACK_DEPTH 96   // traversal stack entries (traverse.cuh); Karras trees are bounded by key + index bits, PLOC trees are checked at build
+
 struct DeviceScene {
     int device = -1;
     SceneView view{};

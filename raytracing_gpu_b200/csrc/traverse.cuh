@@ -9,7 +9,7 @@
 
 namespace rtb {
 
-#define RT_STACK 96   // LBVH depth bound: 63 key bits + index bits for duplicate keys
+#define RT_STACK RT_STACK_DEPTH   // Karras depth bound: 63 key bits + index bits for duplicate keys; PLOC depth is checked at build
 
 struct Closest {
     float t;     // +inf on miss
