@@ -92,6 +92,42 @@ __device__ Box world_box(const SceneView& sv, const DPrim& p, float t_lo, float 
     return b;
 }
 
+// world box of one constant_medium: its boundary primitives through their own chains, then through the medium's
+__device__ void apply_chain_to_box(const SceneView& sv, uint32_t chain, Box& b) {
+    if (!chain) return;
+    const rt_flat_chain c = sv.chains[chain];
+    for (int k = (int)c.count - 1; k >= 0; k--) {
+        const rt_flat_xop op = sv.xops[c.first + k];
+        if (op.kind == RT_XOP_TRANSLATE) {
+            b.lo.x += op.a; b.lo.y += op.b; b.lo.z += op.c; b.hi.x += op.a; b.hi.y += op.b; b.hi.z += op.c;
+        } else {
+            Box r = empty_box();
+            for (int corner = 0; corner < 8; corner++) {
+                const float x = (corner & 1) ? b.hi.x : b.lo.x, y = (corner & 2) ? b.hi.y : b.lo.y, z = (corner & 4) ? b.hi.z : b.lo.z;
+                grow(r, op.b * x + op.a * z, y, -op.a * x + op.b * z);   // hittable.h:131-132
+            }
+            b = r;
+        }
+    }
+}
+
+__global__ void k_medium_bounds(SceneView sv, DMedium* media, uint32_t n_media, float t_lo, float t_hi) {
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n_media) return;
+    DMedium med = media[m];
+    Box all = empty_box();
+    for (uint32_t i = 0; i < med.bprim_count; i++) {
+        const Box b = world_box(sv, sv.bprims[med.bprim_first + i], t_lo, t_hi);   // through the boundary primitive's own chain (padded)
+        all.lo.x = fminf(all.lo.x, b.lo.x); all.lo.y = fminf(all.lo.y, b.lo.y); all.lo.z = fminf(all.lo.z, b.lo.z);
+        all.hi.x = fmaxf(all.hi.x, b.hi.x); all.hi.y = fmaxf(all.hi.y, b.hi.y); all.hi.z = fmaxf(all.hi.z, b.hi.z);
+    }
+    apply_chain_to_box(sv, med.chain, all);
+    const float mx = fmaxf(fmaxf(fmaxf(fabsf(all.lo.x), fabsf(all.hi.x)), fmaxf(fabsf(all.lo.y), fabsf(all.hi.y))), fmaxf(fabsf(all.lo.z), fabsf(all.hi.z)));
+    const float pad = 1e-3f + 1.6e-5f * mx;      // two more transform levels of rounding than a primitive box
+    media[m].lo = make_float4(all.lo.x - pad, all.lo.y - pad, all.lo.z - pad, 0.f);
+    media[m].hi = make_float4(all.hi.x + pad, all.hi.y + pad, all.hi.z + pad, 0.f);
+}
+
 // order-preserving float <-> uint mapping for atomicMin / atomicMax
 __device__ __forceinline__ uint32_t f2ord(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
 __host__ __device__ __forceinline__ float ord2f(uint32_t o) {
@@ -497,6 +533,14 @@ __global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_merge(const int* nn, int n,
 template <class T> cudaError_t dalloc(T** p, size_t count) { return cudaMalloc((void**)p, (count ? count : 1) * sizeof(T)); }
 
 } // namespace
+
+int compute_medium_bounds(DeviceScene& ds, float time_lo, float time_hi, cudaStream_t stream) {
+    if (!ds.view.n_media) return RT_OK;
+    k_medium_bounds<<<(ds.view.n_media + 63) / 64, 64, 0, stream>>>(ds.view, (DMedium*)ds.d_media, ds.view.n_media, time_lo, time_hi);
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaStreamSynchronize(stream));
+    return RT_OK;
+}
 
 int build_lbvh(DeviceScene& ds, const DPrim* d_prims_in, const uint32_t* d_leaf_ids_in, uint32_t n, float time_lo, float time_hi,
                cudaStream_t stream) {

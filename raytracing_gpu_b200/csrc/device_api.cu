@@ -74,7 +74,8 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     std::vector<DMedium> media(fs.media.size());
     for (size_t i = 0; i < fs.media.size(); i++) {
         const rt_flat_medium& m = fs.media[i];
-        media[i] = DMedium{m.chain, m.bprim_first, m.bprim_count, m.material, m.leaf_id, m.neg_inv_density, 0, 0};
+        media[i] = DMedium{m.chain, m.bprim_first, m.bprim_count, m.material, m.leaf_id, m.neg_inv_density, 0, 0,
+                           make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
     }
     // A constant_medium whose boundary is ONE sphere can never report a hit under the reference's semantics
     // (SURVEY Q1/Q2): its second boundary query (constant_medium.h:39, t_min = t1 + 0.0001) meets the same near
@@ -152,6 +153,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     RT_CUDA(cudaEventRecord(b0, st));
     rc = build_lbvh(ds, (const DPrim*)d_prims_in, (const uint32_t*)d_leaf_in, v.n_prims, t_lo, t_hi, st);
     if (rc < 0) return rc;
+    if ((rc = compute_medium_bounds(ds, t_lo, t_hi, st)) < 0) return rc;
     RT_CUDA(cudaEventRecord(b1, st));
     RT_CUDA(cudaStreamSynchronize(st));
     cudaFree(d_prims_in); cudaFree(d_leaf_in);

@@ -24,11 +24,13 @@ struct __align__(16) DPrim {
 };
 static_assert(sizeof(DPrim) == 48, "DPrim must be 48 bytes");
 
-struct __align__(16) DMedium {   // 32 B
+struct __align__(16) DMedium {   // 64 B
     uint32_t chain, bprim_first, bprim_count, material;
     uint32_t leaf_id;
     float neg_inv_density;
     uint32_t pad0, pad1;
+    float4 lo, hi;   // world-space box of the boundary (padded), filled on the device at commit: a ray whose LINE misses it
+                     // cannot cross the boundary at any t, so constant_medium::hit's first boundary query (-inf, +inf) fails
 };
 
 // Binary BVH node in the traversal layout: the PARENT holds both children's boxes, so one 64-byte fetch
@@ -98,6 +100,9 @@ bool cuda_fail(cudaError_t e, const char* what, const char* file, int line);   /
 // bvh_build.cu: builds the LBVH over `prims` (device, flatten order) and returns them reordered.
 int build_lbvh(DeviceScene& ds, const DPrim* d_prims_in, const uint32_t* d_leaf_ids_in, uint32_t n,
                float time_lo, float time_hi, cudaStream_t stream);
+
+// bvh_build.cu: fills DMedium::lo / hi of every medium (in place, device)
+int compute_medium_bounds(DeviceScene& ds, float time_lo, float time_hi, cudaStream_t stream);
 
 // wavefront.cu
 void render_pool_destroy(struct RenderPool* p);

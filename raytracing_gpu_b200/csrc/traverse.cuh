@@ -140,10 +140,22 @@ __device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& r
                                                TraversalCounters* cnt, bool active = true) {
     Closest best; best.t = INFINITY; best.prim = -1;
     closest_surface<COUNT, PARKED>(sv, ray, t_min, best, cnt, active);
-    if (with_media && active) {
+    if (with_media && active && sv.n_active_media) {
+        const float tiny = 1e-20f;
+        const float ix = 1.0f / (fabsf(ray.d.x) < tiny ? copysignf(tiny, ray.d.x) : ray.d.x);
+        const float iy = 1.0f / (fabsf(ray.d.y) < tiny ? copysignf(tiny, ray.d.y) : ray.d.y);
+        const float iz = 1.0f / (fabsf(ray.d.z) < tiny ? copysignf(tiny, ray.d.z) : ray.d.z);
+        const float ox = ray.o.x * ix, oy = ray.o.y * iy, oz = ray.o.z * iz;
         for (uint32_t a = 0; a < sv.n_active_media; a++) {
             const uint32_t m = sv.active_media[a];
             const DMedium med = sv.media[m];
+            {   // the ray's LINE against the medium's world box: a miss means no boundary crossing at any t
+                const float x0 = fmaf(med.lo.x, ix, -ox), x1 = fmaf(med.hi.x, ix, -ox), y0 = fmaf(med.lo.y, iy, -oy), y1 = fmaf(med.hi.y, iy, -oy);
+                const float z0 = fmaf(med.lo.z, iz, -oz), z1 = fmaf(med.hi.z, iz, -oz);
+                const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+                const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+                if (!(tn <= tf)) continue;
+            }
             float t;
             if (medium_t(sv, med, ray, t_min, best.t, [&]() { return xi_of(m); }, t)) { best.t = t; best.prim = -2 - (int)m; }
         }
