@@ -159,7 +159,7 @@ int main(int argc, char** argv) {
     double mean[3] = {0, 0, 0};
     size_t bad = 0;
     for (const vec3& c : host) {
-        if (!(c.x() == c.x()) || !(c.y() == c.y()) || !(c.z() == c.z())) { bad++; continue; }
+        if (!(c.x() == c.x()) || !(c.y() == c.y()) || !(c.z() == c.z()) || fabsf(c.x()) > 1e30f || fabsf(c.y()) > 1e30f || fabsf(c.z()) > 1e30f) { bad++; continue; }   // NaN / inf pixels are counted, not averaged
         mean[0] += c.x(); mean[1] += c.y(); mean[2] += c.z();
     }
     for (double& m : mean) m /= (double)settings.num_pixels;
@@ -169,6 +169,7 @@ int main(int argc, char** argv) {
         if (f) { fwrite(host.data(), sizeof(vec3), host.size(), f); fclose(f); }
     }
     const double samples = (double)settings.num_pixels * spp;
+    for (double& m : mean) if (!(m == m) || m > 1e300 || m < -1e300) m = -1.0;      // keep the line valid JSON (mean over the non-NaN pixels; -1 = not finite)
     printf("{\"impl\": \"reference_cuda\", \"scene\": \"%s\", \"width\": %u, \"height\": %u, \"spp\": %d, \"max_depth\": %d, "
            "\"ms_build\": %.3f, \"ms_render_init\": %.3f, \"ms_render\": %.3f, \"msamples_per_s\": %.6f, "
            "\"image_mean\": [%.6f, %.6f, %.6f], \"nan_pixels\": %zu}\n",

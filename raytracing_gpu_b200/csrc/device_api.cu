@@ -197,10 +197,16 @@ extern "C" int rt_scene_commit(rt_scene* s, int device, rt_build_stats* stats) {
         if (r < 0) { set_error(e); return r; }
     }
     DeviceScene*& slot = device_of(s);
-    if (slot) { device_scene_destroy(slot); slot = nullptr; }
+    RenderPool* kept_pool = nullptr;      // the wavefront pools (hundreds of MB) survive a re-commit on the same device
+    int kept_device = -1;
+    if (slot) { kept_pool = slot->pool; kept_device = slot->device; slot->pool = nullptr; device_scene_destroy(slot); slot = nullptr; }
     DeviceScene* ds = new DeviceScene;
     const int rc = commit_impl(hs, *ds, device);
+    if (rc < 0 || kept_device != device) {
+        if (kept_pool) { if (kept_device >= 0) cudaSetDevice(kept_device); render_pool_destroy(kept_pool); kept_pool = nullptr; }
+    }
     if (rc < 0) { device_scene_destroy(ds); return rc; }
+    ds->pool = kept_pool;
     slot = ds;
     if (stats) *stats = ds->build;
     return RT_OK;

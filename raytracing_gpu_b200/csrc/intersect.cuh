@@ -218,13 +218,20 @@ __device__ __forceinline__ void prim_attr(const SceneView& sv, const DPrim& p, c
 }
 
 // ---- constant_medium::hit — constant_medium.h:34-70 -------------------------------------------------
-// closest hit over a medium's boundary primitives, list semantics (hittable_list.h:23-39: later wins ties)
-__device__ __forceinline__ bool boundary_t(const SceneView& sv, const DMedium& m, const Ray& r, float t_min, float t_max, float& t) {
+// closest hit over a medium's boundary primitives, list semantics (hittable_list.h:23-39: later wins ties).
+// The boundary primitives of one medium nearly always share ONE wrapper chain (a box under translate(rotate_y)),
+// so the object-space ray is cached per chain across the primitives and across both boundary queries.
+struct ChainCache { uint32_t chain; Ray ray; };
+
+__device__ __forceinline__ bool boundary_t(const SceneView& sv, const DMedium& m, const Ray& r, ChainCache& cc, float t_min, float t_max, float& t) {
     bool any = false;
     float closest = t_max;
     for (uint32_t i = 0; i < m.bprim_count; i++) {
+        const DPrim p = sv.bprims[m.bprim_first + i];
+        const uint32_t chain = prim_chain(p);
+        if (chain != cc.chain) { cc.ray = to_object_space(sv, chain, r); cc.chain = chain; }
         float tt;
-        if (prim_t(sv, sv.bprims[m.bprim_first + i], r, t_min, closest, tt)) { any = true; closest = tt; }
+        if (prim_t_local(p, cc.ray, t_min, closest, tt)) { any = true; closest = tt; }
     }
     t = closest;
     return any;
@@ -235,9 +242,10 @@ __device__ __forceinline__ bool boundary_t(const SceneView& sv, const DMedium& m
 template <class XiFn>
 __device__ __forceinline__ bool medium_t(const SceneView& sv, const DMedium& m, const Ray& world, float t_min, float t_max, XiFn&& xi, float& t) {
     const Ray r = to_object_space(sv, m.chain, world);
+    ChainCache cc; cc.chain = 0; cc.ray = r;
     float t1, t2;
-    if (!boundary_t(sv, m, r, -INFINITY, INFINITY, t1)) return false;
-    if (!boundary_t(sv, m, r, t1 + 0.0001f, INFINITY, t2)) return false;
+    if (!boundary_t(sv, m, r, cc, -INFINITY, INFINITY, t1)) return false;
+    if (!boundary_t(sv, m, r, cc, t1 + 0.0001f, INFINITY, t2)) return false;
     if (t1 < t_min) t1 = t_min;
     if (t2 > t_max) t2 = t_max;
     if (t1 >= t2) return false;
