@@ -8,7 +8,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 def lib_path():
-    return os.path.join(_HERE, "librt_b200.so")
+    """The product library.  RT_B200_LIB selects another build of the SAME sources (A/B of compile-time variants)."""
+    return os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 
 
 class RtError(RuntimeError):

@@ -77,7 +77,9 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
                 if (node < 0 && node != RT_NODE_DONE && parked == RT_NODE_DONE) { parked = node; node = pop(); }
             }
             const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
-            if (__any_sync(0xffffffffu, blocked) || !__any_sync(0xffffffffu, node >= 0)) {
+            // one warp reduction answers both questions: bit 1 = some lane is blocked, bit 0 = some lane still has a node
+            const uint32_t state = __reduce_or_sync(0xffffffffu, (blocked ? 2u : 0u) | (node >= 0 ? 1u : 0u));
+            if (state != 1u) {
                 if (parked != RT_NODE_DONE) {
                     const int prim = ~parked;
                     parked = RT_NODE_DONE;

@@ -91,6 +91,9 @@ struct FrameParams {
 };
 
 constexpr int EXTEND_BLOCK = 128;
+#ifndef EXTEND_MIN_BLOCKS
+#define EXTEND_MIN_BLOCKS 8
+#endif
 
 // work index -> pool position: bounced paths first, fresh camera paths at the top end of the pool
 __device__ __forceinline__ uint32_t pos_of(uint32_t idx, uint32_t n_bounce, uint32_t n, uint32_t capacity) {
@@ -164,7 +167,7 @@ __global__ void __launch_bounds__(256) k_generate(SceneView sv, PoolView pv, Fra
 
 // ---- extend ---------------------------------------------------------------------------------------
 template <bool COUNT, bool PARKED = false>
-__global__ void __launch_bounds__(EXTEND_BLOCK) k_extend(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+__global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(SceneView sv, PoolView pv, FrameParams fp, int cur) {
     const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
     const uint32_t lane = threadIdx.x & 31;
     const float4* __restrict__ ray_o = pv.ray_o[cur];

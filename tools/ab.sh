@@ -1,4 +1,3 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-python tools/bvh_probe.py cornell_smoke 64 2>&1 | grep -v Warn
-python bench.py --spp 256 --steps 2 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']), round(d['ms_per_step'],1), d['e2e']['value'])"
+run() { python bench.py --spp 128 --steps 2 --warmup 3 --no-cpu-baseline --no-e2e 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); k=d['roofline']['kernel_ms_per_step']; print('$1', round(d['value']), round(d['ms_per_step'],1), round(k['extend'],1), round(k['shade'],1))"; }
+for i in 1 2; do run nb8; RT_B200_LIB=$PWD/raytracing_gpu_b200/librt_b200_nb6.so run nb6; RT_B200_LIB=$PWD/raytracing_gpu_b200/librt_b200_nb4.so run nb4; done
