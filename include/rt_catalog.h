@@ -16,6 +16,11 @@ typedef struct rt_catalog_params {
     /* "mesh": flat arrays as create_meshes_d takes them + camera (lookfrom, lookat, vup, vfov, aspect, aperture, focus, t0, t1) */
     const float* vertices; int n_vertices; const uint32_t* indices; int n_triangles; const float* uvs; const float* normals;
     const float* camera15;
+    /* RNG-built scenes (big1; the Perlin tables of two_perlin / final): draws the reference passes as function ARGUMENTS
+     * (scenes.h:152, vec3.h:63/:68) are taken in nvcc's left-to-right order by default, i.e. the scene the reference's
+     * CUDA build constructs on the device; 1 = the host compiler's order (what a g++ build of the same sources gives,
+     * used to pin the catalogue against oracle/_ref). */
+    int host_argument_order;
 } rt_catalog_params;
 
 /* names: basic, first, big1, two_spheres, two_perlin, earth, cornell, cornell_smoke, triangle, triangles, mesh, final.

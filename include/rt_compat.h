@@ -78,14 +78,30 @@ struct vec3 {
     float length_squared() const { return e[0] * e[0] + e[1] * e[1] + e[2] * e[2]; }
     float length() const { return sqrtf(length_squared()); }
     bool near_zero() const { const float s = 1e-6f; return (fabsf(e[0]) < s) && (fabsf(e[1]) < s) && (fabsf(e[2]) < s); }
-    // argument evaluation order is the compiler's, as in the reference (vec3.h:62-69)
-    static vec3 random(curandState* s) { return vec3(random_float(s), random_float(s), random_float(s)); }
-    static vec3 random(curandState* s, const float min, const float max) {
-        return vec3(random_float(s, min, max), random_float(s, min, max), random_float(s, min, max));
-    }
+    // vec3.h:62-69 passes three draws as constructor arguments, whose evaluation order C++ leaves to the compiler
+    // (SURVEY §3.4): nvcc's device code — what the reference actually runs — evaluates left to right (x first), g++
+    // right to left (z first).  rtc::device_argument_order() selects nvcc's order explicitly; otherwise the expression
+    // is the reference's own and the order is the host compiler's.
+    static inline vec3 random(curandState* s);
+    static inline vec3 random(curandState* s, const float min, const float max);
 };
 using point3 = vec3;
 using color = vec3;
+
+namespace rtc {
+// true: draws that the reference passes as function arguments are taken in nvcc's (left-to-right) order, so
+// RNG-built scenes equal what the reference's CUDA build constructs on the device (checked against that build on the
+// B200: tests/test_gpu.py::test_reference_cuda_build_agrees_on_first_hits).  false: the host compiler's order.
+inline bool& device_argument_order() { static thread_local bool f = false; return f; }
+}
+inline vec3 vec3::random(curandState* s) {
+    if (rtc::device_argument_order()) { const float x = random_float(s); const float y = random_float(s); const float z = random_float(s); return vec3(x, y, z); }
+    return vec3(random_float(s), random_float(s), random_float(s));
+}
+inline vec3 vec3::random(curandState* s, const float min, const float max) {
+    if (rtc::device_argument_order()) { const float x = random_float(s, min, max); const float y = random_float(s, min, max); const float z = random_float(s, min, max); return vec3(x, y, z); }
+    return vec3(random_float(s, min, max), random_float(s, min, max), random_float(s, min, max));
+}
 
 inline vec3 operator+(const vec3& u, const vec3& v) { return vec3(u.e[0] + v.e[0], u.e[1] + v.e[1], u.e[2] + v.e[2]); }
 inline vec3 operator-(const vec3& u, const vec3& v) { return vec3(u.e[0] - v.e[0], u.e[1] - v.e[1], u.e[2] - v.e[2]); }

@@ -10,7 +10,8 @@
  * reference's device constructors inside a <<<1,1>>> builder kernel, exactly like the reference's own
  * create_*_world kernels and in the same order as oracle/ref_harness.cpp::build_final.
  *
- * usage: ref_cuda <big1|cornell_smoke|cornell|final> <width> <spp> <max_depth> [earth.rgb8 w h]
+ * usage: ref_cuda <big1|cornell_smoke|cornell|final> <width> <spp> <max_depth> [earth.rgb8 w h] [image_out.f32]
+ *        ref_cuda <scene> probe <rays.f32 (n x 7)> <out.f32 (n t values, then n x 3 normals)> [earth.rgb8 w h]
  * prints one JSON line.  Only bench.py's reference legs and tests/ may execute it.
  * Everything in this file is harness code written for this repo; no reference code is copied.
  */
@@ -94,6 +95,49 @@ struct final_scene : public scene {
     }
 };
 
+/* Route-B probe: the reference's own device intersection code asked for the closest hit of caller-supplied
+ * rays, exactly as color_f does at render.h:63.  One thread per ray; t = +inf on a miss.  constant_medium draws from the
+ * per-thread cuRAND state, so media hits are stochastic: compare those scenes on surface hits only. */
+__global__ void probe_first_hit(hittable** world, const float* rays, int n, float* out_t, float* out_normal) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    curandState rs;
+    curand_init(1984, i, 0, &rs);
+    const float* q = rays + 7 * (size_t)i;
+    ray r(point3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]), q[6]);
+    hit_record rec;
+    const bool hit = (*world)->hit(r, 0.001f, infinity, rec, &rs);
+    out_t[i] = hit ? rec.t : infinity;
+    out_normal[3 * i] = hit ? rec.normal.x() : 0.f; out_normal[3 * i + 1] = hit ? rec.normal.y() : 0.f; out_normal[3 * i + 2] = hit ? rec.normal.z() : 0.f;
+}
+
+static int run_probe(scene* sc, const char* rays_path, const char* out_path) {
+    FILE* f = fopen(rays_path, "rb");
+    if (!f) { fprintf(stderr, "cannot read %s\n", rays_path); return 2; }
+    fseek(f, 0, SEEK_END); const long bytes = ftell(f); fseek(f, 0, SEEK_SET);
+    const int n = (int)(bytes / (7 * sizeof(float)));
+    std::vector<float> rays((size_t)n * 7), t(n), nrm((size_t)n * 3);
+    if (fread(rays.data(), sizeof(float), rays.size(), f) != rays.size()) { fclose(f); return 2; }
+    fclose(f);
+    float *d_rays, *d_t, *d_n;
+    checkCudaErrors(cudaMalloc((void**)&d_rays, rays.size() * sizeof(float)));
+    checkCudaErrors(cudaMalloc((void**)&d_t, n * sizeof(float)));
+    checkCudaErrors(cudaMalloc((void**)&d_n, 3 * (size_t)n * sizeof(float)));
+    checkCudaErrors(cudaMemcpy(d_rays, rays.data(), rays.size() * sizeof(float), cudaMemcpyHostToDevice));
+    probe_first_hit<<<(n + 63) / 64, 64>>>(sc->d_world, d_rays, n, d_t, d_n);
+    checkCudaErrors(cudaGetLastError());
+    checkCudaErrors(cudaDeviceSynchronize());
+    checkCudaErrors(cudaMemcpy(t.data(), d_t, n * sizeof(float), cudaMemcpyDeviceToHost));
+    checkCudaErrors(cudaMemcpy(nrm.data(), d_n, 3 * (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+    f = fopen(out_path, "wb");
+    if (!f) return 2;
+    fwrite(t.data(), sizeof(float), t.size(), f);
+    fwrite(nrm.data(), sizeof(float), nrm.size(), f);
+    fclose(f);
+    printf("{\"impl\": \"reference_cuda\", \"mode\": \"probe\", \"rays\": %d}\n", n);
+    return 0;
+}
+
 static double wall_ms() {
     timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
@@ -103,7 +147,8 @@ static double wall_ms() {
 int main(int argc, char** argv) {
     if (argc < 5) { fprintf(stderr, "usage: %s <big1|cornell_smoke|cornell|final> <width> <spp> <max_depth> [earth.rgb8 w h]\n", argv[0]); return 2; }
     const std::string name = argv[1];
-    const int width = atoi(argv[2]), spp = atoi(argv[3]), max_depth = atoi(argv[4]);
+    const bool probe = std::string(argv[2]) == "probe";
+    const int width = probe ? 16 : atoi(argv[2]), spp = probe ? 1 : atoi(argv[3]), max_depth = probe ? 1 : atoi(argv[4]);
     // the reference never raises these: bvh_node::hit allocates per ray, merge() leaks during the build
     checkCudaErrors(cudaDeviceSetLimit(cudaLimitMallocHeapSize, (size_t)4 << 30));
     checkCudaErrors(cudaDeviceSetLimit(cudaLimitStackSize, 8192));
@@ -124,6 +169,7 @@ int main(int argc, char** argv) {
     } else { fprintf(stderr, "unknown scene %s\n", name.c_str()); return 2; }
     checkCudaErrors(cudaDeviceSynchronize());
     const double ms_build = wall_ms() - t_build0;
+    if (probe) return run_probe(sc, argv[3], argv[4]);
 
     render_settings settings;                      // render.h:21-50
     settings.aspect_ratio = sc->aspect;

@@ -40,7 +40,7 @@ class BuildStats(C.Structure):
 class CatalogParams(C.Structure):
     _fields_ = [("image", C.c_void_p), ("image_width", C.c_int), ("image_height", C.c_int), ("image_bytes_per_pixel", C.c_int),
                 ("aspect", C.c_float), ("vertices", C.c_void_p), ("n_vertices", C.c_int), ("indices", C.c_void_p),
-                ("n_triangles", C.c_int), ("uvs", C.c_void_p), ("normals", C.c_void_p), ("camera15", C.c_void_p)]
+                ("n_triangles", C.c_int), ("uvs", C.c_void_p), ("normals", C.c_void_p), ("camera15", C.c_void_p), ("host_argument_order", C.c_int)]
 
 
 class DrawSettings(C.Structure):
@@ -237,11 +237,13 @@ class Scene:
         return _check(lib().rt_set_camera_raw(self._h, c.ctypes.data))
 
     @staticmethod
-    def from_catalog(name, image=None, aspect=0.0, mesh=None, camera15=None):
+    def from_catalog(name, image=None, aspect=0.0, mesh=None, camera15=None, host_argument_order=False):
         """Library scene (include/rt_catalog.h).  image: (H, W, 3|4) uint8; mesh: (vertices, indices, uvs, normals).
+        host_argument_order: RNG draws passed as function arguments in the host compiler's order instead of nvcc's.
         Returns (scene, aspect_ratio)."""
         sc = Scene()
         p = CatalogParams()
+        p.host_argument_order = 1 if host_argument_order else 0
         keep = []
         if image is not None:
             img = np.ascontiguousarray(image, dtype=np.uint8)

@@ -53,7 +53,11 @@ Built big1() {                                                    // scenes.h:14
     for (int a = -11; a < 11; a++)
         for (int b = -11; b < 11; b++) {
             const float choose_mat = random_float(rs);
-            const point3 center(a + 0.9f * random_float(rs), 0.2f, b + 0.9f * random_float(rs));   // argument order: the compiler's, as in scenes.h:152
+            point3 center;
+            if (rtc::device_argument_order()) {   // scenes.h:152 passes both draws as constructor arguments: nvcc takes x first
+                const float cx = a + 0.9f * random_float(rs); const float cz = b + 0.9f * random_float(rs);
+                center = point3(cx, 0.2f, cz);
+            } else center = point3(a + 0.9f * random_float(rs), 0.2f, b + 0.9f * random_float(rs));   // the host compiler's order
             if ((center - point3(4, 0.2, 0)).length_squared() > 0.9f * 0.9f) {
                 if (choose_mat < 0.8) {
                     const color albedo = color::random(rs) * color::random(rs);
@@ -213,6 +217,8 @@ extern "C" int rt_catalog_scene(rt_scene* s, const char* name, const rt_catalog_
     if (!s || !name) { rtb::set_error("catalog: null argument"); return RT_ERR_INVALID; }
     try {
         rtc::scope bind(s);
+        struct OrderGuard { bool prev; OrderGuard(bool v) : prev(rtc::device_argument_order()) { rtc::device_argument_order() = v; }
+                            ~OrderGuard() { rtc::device_argument_order() = prev; } } order(!(p && p->host_argument_order));
         const std::string n(name);
         Built b;
         if (n == "basic") b = basic();

@@ -231,3 +231,26 @@ def assert_first_hit_parity(blob, ids, t, want_ids, want_t):
     np.testing.assert_array_equal(t[~med].view(np.uint32), want_t[~med].view(np.uint32))
     if med.any():
         np.testing.assert_allclose(t[med], want_t[med], rtol=1e-6, atol=0)
+
+
+def ref_cuda_probe(scene_name, rays, image=None, exe="ref_cuda_nofma"):
+    """First-hit distances from the REFERENCE's own device code: oracle/_ref/<exe> builds the named scene with the
+    reference's kernels and runs world->hit (hittable_list.h / bvh.h) on `rays` in one CUDA thread per ray.  Returns
+    float32 t (inf = miss), or None when the binary was not built (it is compiled from /root/reference by
+    oracle/Makefile in the authoring container and travels to the GPU box)."""
+    import subprocess
+    import tempfile
+    path = os.path.join(ROOT, "oracle", "_ref", exe)
+    if not os.path.exists(path):
+        return None
+    with tempfile.TemporaryDirectory() as d:
+        rp, op = os.path.join(d, "rays.f32"), os.path.join(d, "out.f32")
+        np.ascontiguousarray(rays, np.float32).tofile(rp)
+        extra = []
+        if image is not None:
+            ip = os.path.join(d, "image.rgb8")
+            np.ascontiguousarray(image, np.uint8).tofile(ip)
+            extra = [ip, str(image.shape[1]), str(image.shape[0])]
+        subprocess.check_call([path, scene_name, "probe", rp, op] + extra, stdout=subprocess.DEVNULL)
+        out = np.fromfile(op, np.float32)
+    return out[:len(rays)]

@@ -12,15 +12,18 @@ from tests import helpers
 REFERENCE = "/root/reference"
 
 
-def catalog_scene(name):
+def catalog_scene(name, host_order=True):
+    """host_order=True: function-argument draws in g++'s order, i.e. the scene oracle/_ref (the reference's sources built
+    by g++) constructs — what the goldens hold.  The library default is nvcc's order (the reference's CUDA build)."""
+    kw = dict(host_argument_order=host_order)
     if name == "earth":
-        return rt.Scene.from_catalog(name, image=helpers.procedural_image(256, 128, seed=11))
+        return rt.Scene.from_catalog(name, image=helpers.procedural_image(256, 128, seed=11), **kw)
     if name == "final":
-        return rt.Scene.from_catalog(name, image=helpers.procedural_image(128, 64, seed=12), aspect=1.0)
+        return rt.Scene.from_catalog(name, image=helpers.procedural_image(128, 64, seed=12), aspect=1.0, **kw)
     if name == "mesh":
         return rt.Scene.from_catalog(name, image=helpers.procedural_image(64, 64, seed=13), mesh=helpers.procedural_mesh(16, 24),
-                                     camera15=helpers.MESH_CAMERA)
-    return rt.Scene.from_catalog(name)
+                                     camera15=helpers.MESH_CAMERA, **kw)
+    return rt.Scene.from_catalog(name, **kw)
 
 
 @pytest.mark.parametrize("name", helpers.NAMED_SCENES + ["earth", "final", "mesh"])
@@ -40,6 +43,31 @@ def test_catalog_scene_equals_reference_built_scene(name):
     a, _ = o.render(16, 9, 2)
     b, _ = o_ref.render(16, 9, 2)
     np.testing.assert_array_equal(a, b)
+
+
+def test_device_argument_order_only_moves_rng_built_scenes():
+    """The default (nvcc's left-to-right order of argument draws) changes exactly the scenes whose geometry or Perlin
+    tables come from argument draws; in big1 it swaps which draw lands in x and which in z of a small sphere."""
+    for name in helpers.NAMED_SCENES:
+        a = catalog_scene(name, host_order=True)[0].export()
+        b = catalog_scene(name, host_order=False)[0].export()
+        same = a.size == b.size and bool((a == b).all())
+        assert same == (name not in ("big1", "two_perlin")), name
+    def centers(host):
+        blob = catalog_scene("big1", host_order=host)[0].export()
+        hdr = np.frombuffer(blob[:16 * 4].tobytes(), np.uint32)
+        n_prims = int(hdr[2])
+        prims = np.frombuffer(blob[176:176 + 64 * n_prims].tobytes(), np.float32).reshape(n_prims, 16)
+        return prims[:, 4:7]                      # f[0..2]: centre
+    ch, cd = centers(True), centers(False)
+    assert ch.shape == cd.shape == (488, 3)
+    np.testing.assert_array_equal(ch[0], cd[0])                         # the ground sphere has no draws
+    moved = np.abs(ch - cd).max(axis=1) > 0
+    assert moved.sum() > 400
+    # the first small sphere: the same two draws, x-jitter and z-jitter swapped between the two orders
+    jitter_h = (ch[1, 0] - (-11), ch[1, 2] - (-11))
+    jitter_d = (cd[1, 0] - (-11), cd[1, 2] - (-11))
+    np.testing.assert_allclose(jitter_h, jitter_d[::-1], rtol=0, atol=2e-6)
 
 
 def test_catalog_errors():
