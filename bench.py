@@ -336,7 +336,8 @@ def main():
     roofline_fp32 = {"bound": "fp32", "achieved": flops / (ms_step * 1e-3) / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
                      "frac": flops / (ms_step * 1e-3) / 1e12 / fp32_peak, "peak_source": "nominal 148 SM x 128 lanes x 2 x max SM clock",
                      "nodes_per_ray": cs.nodes_visited / max(cs.rays, 1), "prim_tests_per_ray": cs.prim_tests / max(cs.rays, 1),
-                     "rays_per_sample": cs.rays / max(cs.samples, 1)}
+                     "rays_per_sample": cs.rays / max(cs.samples, 1),
+                     "warp_lane_utilisation_node_loop": cs.nodes_visited / max(cs.node_slots, 1)}
 
     # end to end through the C-ABI with host buffers: commit (H2D + LBVH build) + render + reduce + D2H
     e2e = None

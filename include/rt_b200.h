@@ -150,7 +150,10 @@ typedef struct rt_render_stats {
     float ms_total;         /* CUDA events, first ray-gen launch -> accumulation complete */
     float ms_generate, ms_extend, ms_shade, ms_finish;
     uint64_t nodes_visited, prim_tests; /* only with RT_RENDER_COUNTERS */
-    uint64_t reserved[4];
+    uint64_t node_slots;    /* with RT_RENDER_COUNTERS: sum over warps of 32 x the longest lane's node steps, i.e. the node
+                               steps the SIMD machine paid for; nodes_visited / node_slots = lane utilisation lost to rays
+                               of one warp finishing at different times */
+    uint64_t reserved[3];
 } rt_render_stats;
 
 /* Render into host memory: out_rgb = width*height*3 floats, linear radiance, mean over the samples rendered

@@ -24,6 +24,16 @@ __device__ __forceinline__ void consider(const SceneView& sv, int prim, float t,
     if (t < best.t || best.prim < 0 || sv.prim_leaf_id[prim] > sv.prim_leaf_id[best.prim]) { best.t = t; best.prim = prim; }
 }
 
+// shared-memory accesses the compiler neither hoists nor keeps in registers (see closest_surface_stream)
+__device__ __forceinline__ float4 lds4(const float4* p) {   // not hoisted, not kept in registers across the node phase
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"((uint32_t)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts4(float4* p, float4 v) {
+    asm volatile("st.shared.v4.f32 [%4], {%0,%1,%2,%3};" :: "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"((uint32_t)__cvta_generic_to_shared(p)) : "memory");
+}
+
 // Two loop shapes (profiles/r01_v4_experiments.md):
 //   PARKED = false  fused node-or-leaf step per iteration.  ncu: 35 % of its issue slots go to the leaf code at
 //                   3.2 active lanes of 32, because almost every iteration SOME lane is at a leaf.
@@ -131,6 +141,150 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     }
 }
 
+// Streaming closest-hit for a persistent warp (k_extend): rays of one warp finish at very different times — measured on
+// the final scene, only 59 % of the node steps a warp pays for carry a live lane (rt_render_stats::node_slots) — so a
+// lane that has finished does not wait for the slowest ray of its batch: once fewer than REFILL_BELOW lanes still walk
+// the tree, every finished lane stores its result and takes the next ray of the queue.  The node step, leaf parking and
+// flush are those of closest_surface<PARKED = true>; one warp reduction per iteration returns the number of walking
+// lanes (low half) and of blocked lanes (high half).
+// Registers: the node phase needs the inverse direction, the t range, node / stack / parked and the node's boxes.
+// Everything else a lane owns — the ray itself, its object-space copy, its pool slot — lives in shared memory
+// (LaneSlots) and is read where a leaf is tested; left in registers it pushes the node phase's operands into local
+// memory (first version: 9 LDL per node step, 45 % slower than the batch kernel).
+//   exchange(fin, fin_mask, valid, best) -> dry     WARP-COLLECTIVE.  Lanes with fin && valid store the result of the ray
+//       they hold (media pass included) and clear valid; finished lanes may receive a new ray (valid = true, ray written
+//       to the lane's slots).  Returns warp-uniform true once the queue can hand out nothing more.
+// The closest hit of a ray does not depend on which lane or warp traces it, nor on what its neighbours do.
+struct LaneSlots {      // this lane's shared-memory slots
+    float4* ray_o;      // origin, time
+    float4* ray_d;      // direction, caller's word
+    float4* obj_o;      // object-space origin, wrapper chain the copy belongs to (0 = none)
+    float4* obj_d;
+    float4* inv_d;      // slab set-up of the node phase: 1 / d and o / d.  Constant per ray, yet RE-READ after every leaf
+    float4* inv_o;      //   phase: that ends their register live range there, so the leaf code's temporaries cannot
+};                      //   push them into local memory (ptxas spills whole live ranges, hot loop included)
+__device__ __forceinline__ Ray lane_ray(const LaneSlots& ls) {
+    const float4 o = lds4(ls.ray_o), d = lds4(ls.ray_d);
+    Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
+    return r;
+}
+
+template <bool COUNT, int REFILL_BELOW, class Exchange>
+__device__ __forceinline__ void closest_surface_stream(const SceneView& sv, float t_min, const LaneSlots ls, Exchange&& exchange,
+                                                       TraversalCounters* cnt, unsigned long long* slots) {
+    Closest best; best.t = INFINITY; best.prim = -1;
+    int stack[RT_STACK];
+    int sp = 0, node = RT_NODE_DONE, parked = RT_NODE_DONE;
+    bool valid = false;                     // this lane holds a ray whose result is not stored yet
+    uint32_t refill_below = REFILL_BELOW;   // 1 once the queue is dry: then only "nobody walks" ends the node phase
+    auto pop = [&]() { return sp ? stack[--sp] : RT_NODE_DONE; };
+    sts4(ls.inv_d, make_float4(0.f, 0.f, 0.f, 0.f));
+    sts4(ls.inv_o, make_float4(0.f, 0.f, 0.f, 0.f));
+    for (;;) {
+        // node phase
+        uint32_t state;
+        bool blocked;
+        const float4 id4 = lds4(ls.inv_d), io4 = lds4(ls.inv_o);
+        const float ix = id4.x, iy = id4.y, iz = id4.z, ox = io4.x, oy = io4.y, oz = io4.z;
+        do {
+            if (node >= 0) {
+                const BNode* np = sv.nodes + node;
+                const float4 n0 = __ldg(&np->n0), n1 = __ldg(&np->n1), n2 = __ldg(&np->n2);
+                const int2 ch = __ldg(reinterpret_cast<const int2*>(&np->child0));
+                if (COUNT) cnt->nodes++;
+                const float c0lox = fmaf(n0.x, ix, -ox), c0hix = fmaf(n0.y, ix, -ox), c0loy = fmaf(n0.z, iy, -oy), c0hiy = fmaf(n0.w, iy, -oy);
+                const float c1lox = fmaf(n1.x, ix, -ox), c1hix = fmaf(n1.y, ix, -ox), c1loy = fmaf(n1.z, iy, -oy), c1hiy = fmaf(n1.w, iy, -oy);
+                const float c0loz = fmaf(n2.x, iz, -oz), c0hiz = fmaf(n2.y, iz, -oz), c1loz = fmaf(n2.z, iz, -oz), c1hiz = fmaf(n2.w, iz, -oz);
+                const float t0n = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
+                const float t0f = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
+                const float t1n = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
+                const float t1f = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), best.t));
+                const bool h0 = t0n <= t0f, h1 = t1n <= t1f;
+                if (h0 && h1) {
+                    const bool swap = t1n < t0n;
+                    stack[sp++] = swap ? ch.x : ch.y;
+                    node = swap ? ch.y : ch.x;
+                } else if (h0) node = ch.x;
+                else if (h1) node = ch.y;
+                else node = pop();
+                if (node < 0 && node != RT_NODE_DONE && parked == RT_NODE_DONE) { parked = node; node = pop(); }
+            }
+            blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
+            state = __reduce_add_sync(0xffffffffu, (blocked ? 0x10000u : 0u) | (node >= 0 ? 1u : 0u));
+            if (COUNT && (state & 0xffffu)) *slots += 32;
+        } while (state - refill_below < 0x10000u - refill_below);   // refill_below <= walking lanes, nobody blocked
+
+        // leaf phase: every parked leaf is tested, blocked lanes park theirs
+        if (parked != RT_NODE_DONE) {
+            const int prim = ~parked;
+            parked = RT_NODE_DONE;
+            const DPrim p = sv.prims[prim];
+            const uint32_t chain = prim_chain(p);
+            Ray r = lane_ray(ls);
+            if (chain) {   // object-space copy: consecutive leaves usually share a wrapper chain
+                const float4 co = lds4(ls.obj_o);
+                if (__float_as_uint(co.w) == chain) {
+                    const float4 cd = lds4(ls.obj_d);
+                    r.o = make_float3(co.x, co.y, co.z); r.d = make_float3(cd.x, cd.y, cd.z);
+                } else {
+                    r = to_object_space(sv, chain, r);
+                    sts4(ls.obj_o, make_float4(r.o.x, r.o.y, r.o.z, __uint_as_float(chain)));
+                    sts4(ls.obj_d, make_float4(r.d.x, r.d.y, r.d.z, 0.f));
+                }
+            }
+            if (COUNT) cnt->prim_tests++;
+            float t;
+            if (prim_t_local(p, r, t_min, best.t, t)) consider(sv, prim, t, best);
+        }
+        if (blocked) { parked = node; node = pop(); }
+        const bool fin = node == RT_NODE_DONE && parked == RT_NODE_DONE;
+        const uint32_t fm = __ballot_sync(0xffffffffu, fin);
+        if (refill_below > 1u ? __popc(fm) > 32 - REFILL_BELOW : fm != 0u) {
+            const bool dry = exchange(fin, fm, valid, best);
+            if (fin && valid) {
+                const Ray r = lane_ray(ls);
+                const float tiny = 1e-20f;
+                const float ix = 1.0f / (fabsf(r.d.x) < tiny ? copysignf(tiny, r.d.x) : r.d.x);
+                const float iy = 1.0f / (fabsf(r.d.y) < tiny ? copysignf(tiny, r.d.y) : r.d.y);
+                const float iz = 1.0f / (fabsf(r.d.z) < tiny ? copysignf(tiny, r.d.z) : r.d.z);
+                sts4(ls.inv_d, make_float4(ix, iy, iz, 0.f));
+                sts4(ls.inv_o, make_float4(r.o.x * ix, r.o.y * iy, r.o.z * iz, 0.f));
+                best.t = INFINITY; best.prim = -1;
+                sts4(ls.obj_o, make_float4(0.f, 0.f, 0.f, 0.f));
+                sp = 0;
+                node = sv.n_prims ? 0 : RT_NODE_DONE;
+            }
+            if (dry) {
+                refill_below = 1u;
+                if (!__any_sync(0xffffffffu, valid)) break;
+            }
+        }
+    }
+}
+
+// The media pass of closest_hit for one lane (not collective).
+template <class XiOf>
+__device__ __forceinline__ void closest_medium(const SceneView& sv, const Ray& ray, float t_min, Closest& best, XiOf&& xi_of) {
+    const float tiny = 1e-20f;
+    const float ix = 1.0f / (fabsf(ray.d.x) < tiny ? copysignf(tiny, ray.d.x) : ray.d.x);
+    const float iy = 1.0f / (fabsf(ray.d.y) < tiny ? copysignf(tiny, ray.d.y) : ray.d.y);
+    const float iz = 1.0f / (fabsf(ray.d.z) < tiny ? copysignf(tiny, ray.d.z) : ray.d.z);
+    const float ox = ray.o.x * ix, oy = ray.o.y * iy, oz = ray.o.z * iz;
+    for (uint32_t a = 0; a < sv.n_active_media; a++) {
+        const uint32_t m = sv.active_media[a];
+        const DMedium med = sv.media[m];
+        {   // the ray's LINE against the medium's world box: a miss means no boundary crossing at any t
+            const float x0 = fmaf(med.lo.x, ix, -ox), x1 = fmaf(med.hi.x, ix, -ox), y0 = fmaf(med.lo.y, iy, -oy), y1 = fmaf(med.hi.y, iy, -oy);
+            const float z0 = fmaf(med.lo.z, iz, -oz), z1 = fmaf(med.hi.z, iz, -oz);
+            const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+            const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+            if (!(tn <= tf)) continue;
+        }
+        float t;
+        if (medium_t(sv, med, ray, t_min, best.t, [&]() { return xi_of(m); }, t)) { best.t = t; best.prim = -2 - (int)m; }
+    }
+}
+
 // Media are evaluated after the surfaces with t_max = closest surface.  In the reference a medium sees only
 // the objects listed BEFORE it (hittable_list.h:29-35); because constant_medium clips its exit to t_max before
 // sampling (constant_medium.h:44) the result is the same except where the sampled distance lands within one
@@ -142,26 +296,7 @@ __device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& r
                                                TraversalCounters* cnt, bool active = true) {
     Closest best; best.t = INFINITY; best.prim = -1;
     closest_surface<COUNT, PARKED>(sv, ray, t_min, best, cnt, active);
-    if (with_media && active && sv.n_active_media) {
-        const float tiny = 1e-20f;
-        const float ix = 1.0f / (fabsf(ray.d.x) < tiny ? copysignf(tiny, ray.d.x) : ray.d.x);
-        const float iy = 1.0f / (fabsf(ray.d.y) < tiny ? copysignf(tiny, ray.d.y) : ray.d.y);
-        const float iz = 1.0f / (fabsf(ray.d.z) < tiny ? copysignf(tiny, ray.d.z) : ray.d.z);
-        const float ox = ray.o.x * ix, oy = ray.o.y * iy, oz = ray.o.z * iz;
-        for (uint32_t a = 0; a < sv.n_active_media; a++) {
-            const uint32_t m = sv.active_media[a];
-            const DMedium med = sv.media[m];
-            {   // the ray's LINE against the medium's world box: a miss means no boundary crossing at any t
-                const float x0 = fmaf(med.lo.x, ix, -ox), x1 = fmaf(med.hi.x, ix, -ox), y0 = fmaf(med.lo.y, iy, -oy), y1 = fmaf(med.hi.y, iy, -oy);
-                const float z0 = fmaf(med.lo.z, iz, -oz), z1 = fmaf(med.hi.z, iz, -oz);
-                const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
-                const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
-                if (!(tn <= tf)) continue;
-            }
-            float t;
-            if (medium_t(sv, med, ray, t_min, best.t, [&]() { return xi_of(m); }, t)) { best.t = t; best.prim = -2 - (int)m; }
-        }
-    }
+    if (with_media && active && sv.n_active_media) closest_medium(sv, ray, t_min, best, xi_of);
     return best;
 }
 

@@ -23,6 +23,7 @@
 #include "shade.cuh"
 #include "traverse.cuh"
 
+#include <cuda_pipeline.h>
 #include <algorithm>
 #include <cstring>
 #include <vector>
@@ -41,7 +42,7 @@ struct __align__(128) Counters {
     uint32_t cur_extend;              uint32_t pad2[31];
     uint32_t cur_shade;               uint32_t pad3[31];
     unsigned long long next_sample;   unsigned long long pad4[15];   // global sample cursor (sample-major: g = sample * npix + pixel)
-    unsigned long long total_rays, nodes, prim_tests;
+    unsigned long long total_rays, nodes, prim_tests, node_slots;
 };
 
 struct PoolView {
@@ -174,11 +175,13 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
     const float4* __restrict__ ray_d = pv.ray_d[cur];
     const float4* thr = pv.thr[cur];
     TraversalCounters tc{0, 0};
+    unsigned long long slots = 0;
     for (;;) {
         const uint32_t base = warp_claim(&pv.c->cur_extend);
         if (base >= n) break;
         const uint32_t idx = base + lane;
         const bool active = idx < n;                // closest_hit is warp-collective
+        const uint32_t nodes_before = tc.nodes;
         const uint32_t pos = pos_of(active ? idx : base, n_b, n, pv.capacity);
         const float4 o = ray_o[pos], d = ray_d[pos];
         Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
@@ -189,6 +192,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
             const RngKey key{__float_as_uint(thr[pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
             return draw4(key, RT_STREAM_MEDIUM, m).x;
         }, &tc, active);
+        if (COUNT) slots += 32ull * __reduce_max_sync(0xffffffffu, tc.nodes - nodes_before);   // node steps the warp paid for
         if (active) {
             int q = Q_MISS;
             if (c.prim != -1) {
@@ -202,6 +206,111 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
     if (COUNT) {
         atomicAdd(&pv.c->nodes, (unsigned long long)tc.nodes);
         atomicAdd(&pv.c->prim_tests, (unsigned long long)tc.prim_tests);
+        if (lane == 0) atomicAdd(&pv.c->node_slots, slots);
+    }
+}
+
+// Streaming variant (closest_surface_stream): finished lanes are refilled from the queue while the rest of the warp
+// keeps walking.  Same results ray by ray; only which lane traces which ray changes.
+// A refill must not cost a round trip to the queue cursor plus one to the pool (both DRAM latencies, paid with most of
+// the warp waiting): every warp keeps a ring of 64 staged rays in shared memory, filled 32 at a time by cp.async from
+// a chunk whose queue position was claimed one refill earlier, so the atomic and the loads are in flight while the
+// warp traverses and a refill reads shared memory only.
+#ifndef RT_REFILL_BELOW
+#define RT_REFILL_BELOW 24
+#endif
+constexpr uint32_t RING = 64, RING_INVALID = 0xffffffffu;
+struct StreamShared {
+    float4 ring_o[EXTEND_BLOCK / 32][RING], ring_d[EXTEND_BLOCK / 32][RING];   // staged rays, per warp
+    float4 lane_o[EXTEND_BLOCK], lane_d[EXTEND_BLOCK];                          // the ray each lane traces (LaneSlots)
+    float4 obj_o[EXTEND_BLOCK], obj_d[EXTEND_BLOCK];
+    float4 inv_d[EXTEND_BLOCK], inv_o[EXTEND_BLOCK];
+    uint32_t ring_pos[EXTEND_BLOCK / 32][RING];
+    uint32_t lane_pos[EXTEND_BLOCK];                                            // its pool slot
+    uint32_t q[EXTEND_BLOCK / 32][4];                                           // per warp: handed out, staged, -, staged all
+};
+template <bool COUNT>
+__global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend_stream(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+    __shared__ StreamShared sh;
+    const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    TraversalCounters tc{0, 0};
+    unsigned long long slots = 0;
+    uint32_t next_base = 0;              // lane 0: queue position of the next chunk to stage, claimed one refill ahead
+    if (lane == 0) {                     // (a register, so that nobody waits for the atomic before the value is needed)
+        sh.q[warp][0] = 0; sh.q[warp][1] = 0; sh.q[warp][3] = 0;
+        next_base = atomicAdd(&pv.c->cur_extend, 32u);
+    }
+    __syncwarp();
+    const LaneSlots ls{&sh.lane_o[threadIdx.x], &sh.lane_d[threadIdx.x], &sh.obj_o[threadIdx.x], &sh.obj_d[threadIdx.x],
+                       &sh.inv_d[threadIdx.x], &sh.inv_o[threadIdx.x]};
+    closest_surface_stream<COUNT, RT_REFILL_BELOW>(sv, 0.001f, ls,                                              // render.h:63
+        [&](bool fin, uint32_t fm, bool& valid, Closest& c) {
+            const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
+            float4* ring_o = sh.ring_o[warp];
+            float4* ring_d = sh.ring_d[warp];
+            uint32_t* ring_pos = sh.ring_pos[warp];
+            volatile uint32_t* q = sh.q[warp];
+            if (fin && valid) {
+                const uint32_t pos = sh.lane_pos[threadIdx.x];
+                if (sv.n_active_media) {
+                    const Ray r = lane_ray(ls);
+                    const uint32_t sb = __float_as_uint(lds4(ls.ray_d).w);
+                    closest_medium(sv, r, 0.001f, c, [&](uint32_t m) {   // free-flight draw keyed (pixel, sample, bounce, m)
+                        const RngKey key{__float_as_uint(pv.thr[cur][pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
+                        return draw4(key, RT_STREAM_MEDIUM, m).x;
+                    });
+                }
+                int qc = Q_MISS;
+                if (c.prim != -1) {
+                    const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
+                    qc = 1 + (int)sv.materials[mat].type;
+                }
+                pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
+                pv.hit_class[pos] = (uint8_t)qc;
+                valid = false;
+            }
+            // hand out staged rays
+            __pipeline_wait_prior(0);
+            __syncwarp();
+            uint32_t head = q[0], tail = q[1];
+            const uint32_t avail = tail - head, want = (uint32_t)__popc(fm), rank = (uint32_t)__popc(fm & lt);
+            if (fin && rank < avail) {
+                const uint32_t slot = (head + rank) & (RING - 1);
+                const uint32_t p = ring_pos[slot];
+                if (p != RING_INVALID) {
+                    sts4(ls.ray_o, lds4(&ring_o[slot]));
+                    sts4(ls.ray_d, lds4(&ring_d[slot]));
+                    sh.lane_pos[threadIdx.x] = p;
+                    valid = true;
+                }
+            }
+            head += min(want, avail);
+            __syncwarp();
+            // stage the chunk claimed earlier, claim the one after it
+            bool staged_all = q[3] != 0;
+            while (!staged_all && tail - head <= RING - 32) {
+                const uint32_t base = __shfl_sync(0xffffffffu, next_base, 0);
+                if (base >= n) { staged_all = true; break; }
+                const uint32_t idx = base + lane, slot = (tail + lane) & (RING - 1);
+                if (idx < n) {
+                    const uint32_t p = pos_of(idx, n_b, n, pv.capacity);
+                    ring_pos[slot] = p;
+                    __pipeline_memcpy_async(&ring_o[slot], &pv.ray_o[cur][p], 16);
+                    __pipeline_memcpy_async(&ring_d[slot], &pv.ray_d[cur][p], 16);
+                } else ring_pos[slot] = RING_INVALID;
+                __pipeline_commit();
+                tail += 32;
+                if (lane == 0) next_base = atomicAdd(&pv.c->cur_extend, 32u);
+            }
+            if (lane == 0) { q[0] = head; q[1] = tail; q[3] = staged_all ? 1u : 0u; }
+            __syncwarp();
+            return staged_all && head == tail;
+        }, &tc, &slots);
+    if (COUNT) {
+        atomicAdd(&pv.c->nodes, (unsigned long long)tc.nodes);
+        atomicAdd(&pv.c->prim_tests, (unsigned long long)tc.prim_tests);
+        if (lane == 0) atomicAdd(&pv.c->node_slots, slots);
     }
 }
 
@@ -445,7 +554,10 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         for (uint64_t it = 0; !done; it++) {
             const int cur = (int)(it & 1);
             if (tick() < 0) return RT_ERR_CUDA;
-            if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            if (fp.pad & 16u) {   // RT_EXP=16: streaming refill
+                if (count) k_extend_stream<true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+                else k_extend_stream<false><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
+            } else if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
             else if (fp.pad & 4u) k_extend<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);   // RT_EXP=4: fused loop
             else k_extend<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
             if (tick() < 0) return RT_ERR_CUDA;
@@ -477,6 +589,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         stats->kernel_launches = launches;
         stats->nodes_visited = P.h_counters->nodes;
         stats->prim_tests = P.h_counters->prim_tests;
+        stats->node_slots = P.h_counters->node_slots;
         cudaEventElapsedTime(&stats->ms_total, P.ev_begin, P.ev_end);
         if (timers) {   // per-kernel device time, summed over the iterations of this frame: 3 events per iteration + 1
             double ext = 0, shd = 0, fin = 0;
