@@ -48,6 +48,7 @@ __device__ __forceinline__ void apply_xop(const rt_flat_xop& op, Ray& r) {
 __device__ __forceinline__ Ray to_object_space(const SceneView& sv, uint32_t chain, Ray r) {
     if (chain) {
         const rt_flat_chain c = sv.chains[chain];
+        #pragma unroll 1   // chains are 1-2 ops long; unrolled copies only cost instruction-cache space
         for (uint32_t k = 0; k < c.count; k++) apply_xop(sv.xops[c.first + k], r);
     }
     return r;
@@ -74,11 +75,15 @@ __device__ __forceinline__ float3 moving_center(const DPrim& p, float time) {   
 }
 
 __device__ __forceinline__ bool rect_t(uint32_t type, const DPrim& p, const Ray& r, float t_min, float t_max, float& t) {
-    // aarect.h:63-75, :94-105, :124-135
-    float tt, a, b;
-    if (type == RT_PRIM_XY_RECT) { tt = (p.b.x - r.o.z) / r.d.z; a = r.o.x + tt * r.d.x; b = r.o.y + tt * r.d.y; }
-    else if (type == RT_PRIM_XZ_RECT) { tt = (p.b.x - r.o.y) / r.d.y; a = r.o.x + tt * r.d.x; b = r.o.z + tt * r.d.z; }
-    else { tt = (p.b.x - r.o.x) / r.d.x; a = r.o.y + tt * r.d.y; b = r.o.z + tt * r.d.z; }
+    // aarect.h:63-75, :94-105, :124-135.  The three orientations differ only in which components play (k, a, b): the
+    // components are selected first so that there is ONE copy of the arithmetic (and of the division) in the kernel —
+    // less code, and rects of different orientation in one warp stay converged
+    const bool xy = type == RT_PRIM_XY_RECT, xz = type == RT_PRIM_XZ_RECT;
+    const float ok = xy ? r.o.z : (xz ? r.o.y : r.o.x), dk = xy ? r.d.z : (xz ? r.d.y : r.d.x);
+    const float oa = (xy | xz) ? r.o.x : r.o.y, da = (xy | xz) ? r.d.x : r.d.y;
+    const float ob = xy ? r.o.y : r.o.z, db = xy ? r.d.y : r.d.z;
+    const float tt = (p.b.x - ok) / dk;
+    const float a = oa + tt * da, b = ob + tt * db;
     if (tt < t_min || tt > t_max) return false;
     if (a < p.a.x || a > p.a.y || b < p.a.z || b > p.a.w) return false;
     t = tt;
@@ -108,8 +113,13 @@ __device__ __forceinline__ bool triangle_t(const DPrim& p, const Ray& r, float t
 // object-space test of one primitive (ray already in the primitive's frame)
 __device__ __forceinline__ bool prim_t_local(const DPrim& p, const Ray& r, float t_min, float t_max, float& t) {
     const uint32_t type = prim_type(p);
-    if (type == RT_PRIM_SPHERE) return sphere_t(f3(p.a.x, p.a.y, p.a.z), p.a.w, r, t_min, t_max, t);
-    if (type == RT_PRIM_MOVING_SPHERE) return sphere_t(moving_center(p, r.tm), p.c0, r, t_min, t_max, t);
+    if (type <= RT_PRIM_MOVING_SPHERE) {   // one copy of the sphere test for both kinds: only centre and radius differ
+        static_assert(RT_PRIM_SPHERE == 0 && RT_PRIM_MOVING_SPHERE == 1, "sphere kinds first");
+        float3 center = f3(p.a.x, p.a.y, p.a.z);
+        float radius = p.a.w;
+        if (type == RT_PRIM_MOVING_SPHERE) { center = moving_center(p, r.tm); radius = p.c0; }
+        return sphere_t(center, radius, r, t_min, t_max, t);
+    }
     if (type == RT_PRIM_TRIANGLE) return triangle_t(p, r, t_min, t_max, t);
     return rect_t(type, p, r, t_min, t_max, t);
 }
@@ -243,9 +253,18 @@ template <class XiFn>
 __device__ __forceinline__ bool medium_t(const SceneView& sv, const DMedium& m, const Ray& world, float t_min, float t_max, XiFn&& xi, float& t) {
     const Ray r = to_object_space(sv, m.chain, world);
     ChainCache cc; cc.chain = 0; cc.ray = r;
-    float t1, t2;
-    if (!boundary_t(sv, m, r, cc, -INFINITY, INFINITY, t1)) return false;
-    if (!boundary_t(sv, m, r, cc, t1 + 0.0001f, INFINITY, t2)) return false;
+    // entry, then exit from just behind the entry (constant_medium.h:33-37).  ONE instance of the boundary code, looped:
+    // k_extend's code size decides its instruction-cache hit rate on scenes with media (profiles/r01_v6_*.md)
+    float tq[2] = {0.f, 0.f};
+    float lo = -INFINITY;
+    #pragma unroll 1
+    for (int q = 0; q < 2; q++) {
+        float tt;
+        if (!boundary_t(sv, m, r, cc, lo, INFINITY, tt)) return false;
+        tq[q] = tt;
+        lo = tt + 0.0001f;
+    }
+    float t1 = tq[0], t2 = tq[1];
     if (t1 < t_min) t1 = t_min;
     if (t2 > t_max) t2 = t_max;
     if (t1 >= t2) return false;

@@ -43,6 +43,7 @@ struct __align__(128) Counters {
     uint32_t cur_shade;               uint32_t pad3[31];
     unsigned long long next_sample;   unsigned long long pad4[15];   // global sample cursor (sample-major: g = sample * npix + pixel)
     unsigned long long total_rays, nodes, prim_tests, node_slots;
+    unsigned long long iter_begin;    // min(next_sample, total) when the current iteration started (written by generate / turnover only)
 };
 
 struct PoolView {
@@ -162,7 +163,7 @@ __device__ __forceinline__ void start_path(const SceneView& sv, const PoolView& 
 // ---- generate: fills the fresh region of pool 0 at the start of a frame ---------------------------
 __global__ void __launch_bounds__(256) k_generate(SceneView sv, PoolView pv, FrameParams fp, uint32_t n_fresh) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) { pv.c->n_fresh[0] = n_fresh; pv.c->next_sample = n_fresh; }
+    if (i == 0) { pv.c->n_fresh[0] = n_fresh; pv.c->next_sample = n_fresh; pv.c->iter_begin = n_fresh; }
     if (i < n_fresh) start_path(sv, pv, fp, 0, pv.capacity - n_fresh + i, i);
 }
 
@@ -335,20 +336,23 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
 
     const int next = cur ^ 1;
     const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
+    const unsigned long long iter_begin = pv.c->iter_begin;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0;
     if (threadIdx.x == 0) s_tile[0] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
     __syncthreads();
+    auto class_of = [&](uint32_t tile) {             // material class of this thread's path in `tile` (NQ past the end)
+        const uint32_t idx = tile + threadIdx.x;
+        return idx < n ? (int)pv.hit_class[pos_of(idx, n_b, n, pv.capacity)] : (int)NQ;
+    };
+    uint32_t tile = s_tile[0];
+    int cls = class_of(tile);
     for (int it = 0;; it ^= 1) {
-        const uint32_t tile = s_tile[it];
         if (tile >= n) break;
 
         // -- sort the tile by material class (counting sort: ballots -> [class][warp] table -> one warp scan)
         {
-            const uint32_t idx = tile + threadIdx.x;
-            int cls = NQ;
-            if (idx < n) cls = pv.hit_class[pos_of(idx, n_b, n, pv.capacity)];
             uint32_t rank = 0;
             #pragma unroll
             for (int k = 0; k < NC; k++) {
@@ -429,19 +433,23 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
                 s_wcont[w] = nc; s_wterm[w] = nt;           // exclusive prefixes
                 nc += a; nt += b;
             }
-            s_base_b = nc ? atomicAdd(&pv.c->n_bounce[next], nc) : 0u;
+            // three INDEPENDENT atomics (one round trip, not three): the fresh region needs no counter of its own —
+            // samples [iter_begin, next_sample) are regenerated in this iteration, so a block's offset in the region
+            // is g0 - iter_begin and k_turnover derives n_fresh from the cursor
+            const uint32_t tile_next = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
+            const uint32_t base_b = nc ? atomicAdd(&pv.c->n_bounce[next], nc) : 0u;
+            const unsigned long long g0 = nt ? atomicAdd(&pv.c->next_sample, (unsigned long long)nt) : 0ull;
             uint32_t n_regen = 0;
-            unsigned long long g0 = 0;
-            if (nt) {
-                g0 = atomicAdd(&pv.c->next_sample, (unsigned long long)nt);
-                if (g0 < fp.total_samples) n_regen = (uint32_t)min((unsigned long long)nt, fp.total_samples - g0);
-            }
-            s_base_f = n_regen ? atomicAdd(&pv.c->n_fresh[next], n_regen) : 0u;
+            if (nt && g0 < fp.total_samples) n_regen = (uint32_t)min((unsigned long long)nt, fp.total_samples - g0);
+            s_base_b = base_b;
+            s_base_f = n_regen ? (uint32_t)(g0 - iter_begin) : 0u;
             s_nregen = n_regen;
             s_g0 = g0;
-            s_tile[it ^ 1] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
+            s_tile[it ^ 1] = tile_next;
         }
         __syncthreads();
+        const uint32_t tile_next = s_tile[it ^ 1];
+        const int cls_next = class_of(tile_next);    // in flight while this tile's results are stored
         if (continues) {
             const uint32_t dst = s_base_b + s_wcont[warp] + __popc(mc & lt);
             pv.ray_o[next][dst] = new_o;
@@ -452,14 +460,19 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
             const uint32_t r = s_wterm[warp] + __popc(mt & lt);
             if (r < s_nregen) start_path(sv, pv, fp, next, pv.capacity - (s_base_f + s_nregen) + r, s_g0 + r);
         }
+        tile = tile_next;
+        cls = cls_next;
     }
 }
 
 // ---- turnover -------------------------------------------------------------------------------------
-__global__ void k_turnover(PoolView pv, int cur, uint32_t* live_out) {
+__global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out) {
     Counters* c = pv.c;
     c->total_rays += c->n_bounce[cur] + c->n_fresh[cur];
     c->n_bounce[cur] = 0; c->n_fresh[cur] = 0;
+    const unsigned long long started = min(c->next_sample, total_samples);   // samples regenerated by this iteration's shade
+    c->n_fresh[cur ^ 1] = (uint32_t)(started - c->iter_begin);
+    c->iter_begin = started;
     c->cur_extend = 0; c->cur_shade = 0;
     *live_out = c->n_bounce[cur ^ 1] + c->n_fresh[cur ^ 1];
 }
@@ -564,7 +577,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
             if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, stream>>>(ds.view, P.v, fp, cur);
             else k_shade<256><<<P.grid_shade, 256, 0, stream>>>(ds.view, P.v, fp, cur);
             if (tick() < 0) return RT_ERR_CUDA;
-            k_turnover<<<1, 1, 0, stream>>>(P.v, cur, d_live + (it % POLL_SLOTS));
+            k_turnover<<<1, 1, 0, stream>>>(P.v, cur, fp.total_samples, d_live + (it % POLL_SLOTS));
             RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
             launches += 3;
             iterations++;
