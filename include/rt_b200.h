@@ -86,6 +86,25 @@ int rt_set_camera(rt_scene* s, const float lookfrom[3], const float lookat[3], c
                   float aspect_ratio, float aperture, float focus_dist, float time0, float time1); /* camera.h:18 */
 int rt_set_camera_raw(rt_scene* s, const rt_flat_camera* cam);
 
+/* Semantics switches.  The default, RT_SEM_REFERENCE, reproduces the reference including the quirks its
+ * images depend on; the other bits repair one quirk each and are NOT covered by the parity contract (no reference output
+ * exists for them).  Takes effect at the next rt_scene_commit.
+ *   RT_SEM_SPHERE_FAR_ROOT       sphere / moving_sphere::hit try the far root (-half_b + sqrtd) / a when the near one is out
+ *                                of range, as the book does — the reference repeats the near root (sphere.h:48-55,
+ *                                moving_sphere.h:38-45).  Rays that start inside a sphere then hit its far side
+ *                                (glass refracts on exit, hollow spheres work) and constant_medium with a sphere boundary
+ *                                scatters (constant_medium.h:38-44; Q2) instead of being inert.
+ *   RT_SEM_UNIT_TRIANGLE_NORMALS triangle face and interpolated vertex normals are normalised before set_face_normal
+ *                                (triangle.h:166, :170-173; Q13).
+ * Q3 (xz_rect bounding box, aarect.h:39) needs no switch: the LBVH computes its own boxes. */
+enum rt_semantics {
+    RT_SEM_REFERENCE = 0,
+    RT_SEM_SPHERE_FAR_ROOT = 1,
+    RT_SEM_UNIT_TRIANGLE_NORMALS = 2,
+    RT_SEM_FIXED = 3
+};
+int rt_set_semantics(rt_scene* s, uint32_t semantics);
+
 /* ---- bulk: replay a scene program (include/rt_program.h) through the calls above ---- */
 int rt_scene_replay(rt_scene* s, const uint32_t* words, size_t n_words);
 
@@ -93,6 +112,8 @@ int rt_scene_replay(rt_scene* s, const uint32_t* words, size_t n_words);
 int rt_scene_flatten(rt_scene* s);                          /* returns the number of leaf ids */
 size_t rt_scene_export_size(rt_scene* s);                   /* 0 if not flattened */
 int rt_scene_export(rt_scene* s, void* buf, size_t cap);    /* layout: rt_flat.h */
+/* 64-bit FNV-1a of the exported blob and the semantics word: identifies the scene a checkpoint belongs to. */
+int rt_scene_hash(rt_scene* s, uint64_t* out);
 
 /* image_height = int(width / aspect) in double, as render_settings::calc_height (render.h:32) */
 int rt_image_height(int width, float aspect);
@@ -121,7 +142,13 @@ int rt_first_hit(rt_scene* s, const float* rays, int n, float t_min, const float
 enum rt_render_flags {
     RT_RENDER_DEFAULT = 0,
     RT_RENDER_COUNTERS = 1, /* fill the traversal counters in rt_render_stats (slower) */
-    RT_RENDER_TIMERS = 2    /* CUDA-event time per kernel class (ms_extend / ms_shade / ms_generate / ms_finish) */
+    RT_RENDER_TIMERS = 2,   /* CUDA-event time per kernel class (ms_extend / ms_shade / ms_generate / ms_finish) */
+    RT_RENDER_ACCUMULATE = 4 /* rt_render only — progressive rendering: out_rgb holds SUMS; it is read, the samples of this call
+                                are added, and it is written back un-normalised (divide by the samples rendered so far
+                                to display).  Because every sample's random numbers are keyed by (pixel, sample index), a
+                                frame rendered in slices [0,a) [a,b) ... equals one rendered in one call up to the order of
+                                the float additions; together with rt_checkpoint_save/load (rt_output.h) a render resumes
+                                after a restart */
 };
 
 #define RT_TILE_BLOCK_PIXELS 1024u

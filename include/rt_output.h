@@ -27,6 +27,23 @@ int rt_write_ppm(const char* path, const uint8_t* rgb8, int width, int height);
  * (stored deflate blocks), no libpng / zlib dependency. */
 int rt_write_png(const char* path, const uint8_t* rgb8, int width, int height);
 
+/* ---- progressive rendering checkpoints -------------------------------------------------------------
+ * A checkpoint is the accumulation buffer of rt_render(..., RT_RENDER_ACCUMULATE) plus what is needed to continue it:
+ * which scene (rt_scene_hash), frame size, seed, depth and how many samples per pixel the sums hold.  Resuming = load,
+ * then keep rendering with sample_first = samples_done.  File: 64-byte little-endian header + width*height*3 floats
+ * + FNV-1a of the floats. */
+typedef struct rt_checkpoint_info {
+    uint32_t width, height;
+    uint32_t seed, max_depth;
+    uint32_t samples_done;       /* the sums hold sample indices [0, samples_done) of every pixel */
+    uint32_t reserved0;
+    uint64_t scene_hash;         /* rt_scene_hash of the scene the samples belong to */
+    uint64_t reserved[3];
+} rt_checkpoint_info;
+int rt_checkpoint_save(const char* path, const rt_checkpoint_info* info, const float* sums_rgb);
+/* sums_rgb may be NULL to read the header only; capacity_floats must be >= width*height*3 otherwise. */
+int rt_checkpoint_load(const char* path, rt_checkpoint_info* info, float* sums_rgb, size_t capacity_floats);
+
 typedef struct rt_draw_settings {      /* render_settings, render.h:21-30 */
     uint32_t image_width;              /* default 1200 */
     uint32_t image_height;             /* 0 = int(image_width / aspect_ratio), render.h:32-34 (one row short at 16:9) */

@@ -50,7 +50,16 @@ class DrawSettings(C.Structure):
                 ("seed", C.c_uint32), ("device", C.c_uint32), ("reserved", C.c_uint32 * 8)]
 
 
+class CheckpointInfo(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("seed", C.c_uint32), ("max_depth", C.c_uint32),
+                ("samples_done", C.c_uint32), ("reserved0", C.c_uint32), ("scene_hash", C.c_uint64),
+                ("reserved", C.c_uint64 * 3)]
+
+
 RENDER_COUNTERS = 1
+RENDER_TIMERS = 2
+RENDER_ACCUMULATE = 4
+SEM_REFERENCE, SEM_SPHERE_FAR_ROOT, SEM_UNIT_TRIANGLE_NORMALS, SEM_FIXED = 0, 1, 2, 3
 
 _lib = None
 
@@ -87,6 +96,7 @@ def lib():
         "rt_bvh": (i32, [vp, vp, i32]), "rt_set_world": (i32, [vp, i32]),
         "rt_set_background": (i32, [vp, f32, f32, f32]),
         "rt_set_camera": (i32, [vp, vp, vp, vp, f32, f32, f32, f32, f32, f32]), "rt_set_camera_raw": (i32, [vp, vp]),
+        "rt_set_semantics": (i32, [vp, C.c_uint32]), "rt_scene_hash": (i32, [vp, C.POINTER(C.c_uint64)]),
         "rt_scene_replay": (i32, [vp, vp, C.c_size_t]), "rt_scene_flatten": (i32, [vp]),
         "rt_scene_export_size": (C.c_size_t, [vp]), "rt_scene_export": (i32, [vp, vp, C.c_size_t]),
         "rt_image_height": (i32, [i32, f32]), "rt_scene_commit": (i32, [vp, i32, C.POINTER(BuildStats)]),
@@ -105,6 +115,8 @@ def lib():
         "rt_average_frames": (i32, [vp, i32, i32, i32, vp]), "rt_write_ppm": (i32, [C.c_char_p, vp, i32, i32]),
         "rt_write_png": (i32, [C.c_char_p, vp, i32, i32]),
         "rt_draw": (i32, [vp, C.POINTER(DrawSettings), C.c_char_p, vp, C.POINTER(C.c_uint32), C.POINTER(RenderStats)]),
+        "rt_checkpoint_save": (i32, [C.c_char_p, C.POINTER(CheckpointInfo), vp]),
+        "rt_checkpoint_load": (i32, [C.c_char_p, C.POINTER(CheckpointInfo), vp, C.c_size_t]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)      # AttributeError here means the .so does not export a declared symbol
@@ -301,6 +313,21 @@ class Scene:
         _check(lib().rt_render(self._h, C.byref(st), out.ctypes.data, C.byref(stats)))
         return out, stats
 
+    def scene_hash(self):
+        h = C.c_uint64()
+        _check(lib().rt_scene_hash(self._h, C.byref(h)))
+        return h.value
+
+    def render_into(self, sums, spp_total, sample_first, sample_count, max_depth=50, seed=1984, flags=0, pool_paths=0):
+        """Progressive rendering (RT_RENDER_ACCUMULATE): adds sample indices [sample_first, sample_first + sample_count)
+        of every pixel to `sums` (H x W x 3 float32, modified in place)."""
+        assert sums.dtype == np.float32 and sums.flags["C_CONTIGUOUS"] and sums.ndim == 3 and sums.shape[2] == 3
+        st = RenderSettings(width=sums.shape[1], height=sums.shape[0], samples_per_pixel=spp_total, max_depth=max_depth, seed=seed,
+                            sample_first=sample_first, sample_count=sample_count, flags=flags | RENDER_ACCUMULATE, pool_paths=pool_paths)
+        stats = RenderStats()
+        _check(lib().rt_render(self._h, C.byref(st), sums.ctypes.data, C.byref(stats)))
+        return stats
+
     def draw(self, image_width, aspect_ratio, samples_per_pixel_per_fb, no_fb, max_depth=50, seed=1984, png_path=None,
              image_height=0, device=0):
         """include/rt_output.h rt_draw: the reference's draw() (render.h:118) — batches, 8-bit quantisation, averaging, PNG."""
@@ -323,6 +350,66 @@ class Scene:
         stats = RenderStats()
         _check(lib().rt_render_device(self._h, C.byref(st), C.c_void_p(d_accum_ptr), C.c_void_p(stream or 0), C.byref(stats)))
         return stats
+
+
+class ProgressiveRender:
+    """Progressive / resumable rendering over rt_render(RT_RENDER_ACCUMULATE) and rt_checkpoint_save / _load
+    (include/rt_output.h).  The frame is the same whatever the slicing: sample k of pixel p draws its
+    random numbers from (p, k) alone.
+
+        pr = ProgressiveRender(scene, 640, 360, spp_total=1024)
+        while not pr.done:
+            pr.step(64); pr.save("frame.ckpt")          # display pr.image() in between
+        # after a restart:  pr = ProgressiveRender.resume(scene, "frame.ckpt", spp_total=1024)
+    """
+
+    def __init__(self, scene, width, height, spp_total, max_depth=50, seed=1984):
+        self.scene, self.spp_total, self.max_depth, self.seed = scene, int(spp_total), int(max_depth), int(seed)
+        self.sums = np.zeros((height, width, 3), np.float32)
+        self.samples_done = 0
+
+    @property
+    def done(self):
+        return self.samples_done >= self.spp_total
+
+    def step(self, n_samples):
+        n = min(int(n_samples), self.spp_total - self.samples_done)
+        if n <= 0:
+            return None
+        stats = self.scene.render_into(self.sums, self.spp_total, self.samples_done, n, max_depth=self.max_depth, seed=self.seed)
+        self.samples_done += n
+        return stats
+
+    def image(self):
+        """Linear means over the samples rendered so far (row 0 = bottom, as rt_render)."""
+        if self.samples_done == 0:
+            raise RtError("no samples rendered yet")
+        return (np.float32(1.0) / np.float32(self.samples_done)) * self.sums
+
+    def save(self, path):
+        info = CheckpointInfo(width=self.sums.shape[1], height=self.sums.shape[0], seed=self.seed, max_depth=self.max_depth,
+                              samples_done=self.samples_done, scene_hash=self.scene.scene_hash())
+        _check(lib().rt_checkpoint_save(os.fsencode(path), C.byref(info), self.sums.ctypes.data))
+
+    @staticmethod
+    def peek(path):
+        info = CheckpointInfo()
+        _check(lib().rt_checkpoint_load(os.fsencode(path), C.byref(info), None, 0))
+        return info
+
+    @classmethod
+    def resume(cls, scene, path, spp_total):
+        """Continue the render `path` holds.  Refuses a checkpoint of another scene (rt_scene_hash) or one that already
+        holds more samples than spp_total."""
+        info = cls.peek(path)
+        if info.scene_hash != scene.scene_hash():
+            raise RtError(f"{path}: checkpoint belongs to another scene (or other semantics)")
+        if info.samples_done > spp_total:
+            raise RtError(f"{path}: holds {info.samples_done} samples per pixel, more than spp_total={spp_total}")
+        pr = cls(scene, info.width, info.height, spp_total, max_depth=info.max_depth, seed=info.seed)
+        _check(lib().rt_checkpoint_load(os.fsencode(path), C.byref(info), pr.sums.ctypes.data, pr.sums.size))
+        pr.samples_done = info.samples_done
+        return pr
 
 
 class ObjMesh:

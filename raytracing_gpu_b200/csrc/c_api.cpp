@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <vector>
 
 using namespace rtb;
 
@@ -231,6 +232,29 @@ int rt_bvh(rt_scene* s, const int* children, int n) { return group(s, children, 
 int rt_set_world(rt_scene* s, int h) {
     CHECK_SCENE(s); CHECK_IX(h, s->host.nodes, "hittable");
     s->host.world = h; s->host.flat.valid = false;
+    return RT_OK;
+}
+
+int rt_scene_hash(rt_scene* s, uint64_t* out) {
+    CHECK_SCENE(s);
+    if (!out) return fail(RT_ERR_INVALID, "null out pointer");
+    if (!s->host.flat.valid) { const int rc = rt_scene_flatten(s); if (rc < 0) return rc; }
+    std::vector<uint8_t> blob(s->host.export_size());
+    const int rc = rt_scene_export(s, blob.data(), blob.size());
+    if (rc < 0) return rc;
+    uint64_t h = 1469598103934665603ull;   // FNV-1a
+    auto mix = [&](const uint8_t* p, size_t n) { for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 1099511628211ull; } };
+    mix(blob.data(), blob.size());
+    const uint32_t sem = s->host.semantics;
+    mix(reinterpret_cast<const uint8_t*>(&sem), sizeof(sem));
+    *out = h;
+    return RT_OK;
+}
+
+int rt_set_semantics(rt_scene* s, uint32_t semantics) {
+    CHECK_SCENE(s);
+    if (semantics & ~(uint32_t)RT_SEM_FIXED) return fail(RT_ERR_INVALID, "set_semantics: unknown bits");
+    s->host.semantics = semantics;
     return RT_OK;
 }
 

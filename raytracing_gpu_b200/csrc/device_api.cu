@@ -86,7 +86,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     for (size_t i = 0; i < fs.media.size(); i++) {
         const rt_flat_medium& m = fs.media[i];
         const bool inert = m.bprim_count == 1 && (fs.bprims[m.bprim_first].type == RT_PRIM_SPHERE || fs.bprims[m.bprim_first].type == RT_PRIM_MOVING_SPHERE);
-        if (!inert) active_media.push_back((uint32_t)i);
+        if (!inert || (hs.semantics & RT_SEM_SPHERE_FAR_ROOT)) active_media.push_back((uint32_t)i);   // with the far root they do scatter
     }
     std::vector<DPerlin> perlins(fs.perlins.size());
     for (size_t i = 0; i < fs.perlins.size(); i++) {
@@ -143,6 +143,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     v.active_media = (const uint32_t*)ds.d_active_media; v.n_active_media = (uint32_t)active_media.size();
     v.camera = fs.hdr.camera;
     std::memcpy(v.background, fs.hdr.background, sizeof(v.background));
+    v.semantics = hs.semantics;
     RT_CUDA(cudaEventRecord(e1, st));
 
     // shutter interval the boxes of moving spheres must cover: the camera's, widened to the reference's

@@ -72,7 +72,7 @@ struct SceneView {
     uint32_t n_prims, n_media, n_nodes, n_active_media;
     rt_flat_camera camera;
     float background[3];
-    float pad2;
+    uint32_t semantics;            // rt_semantics bits (rt_b200.h); 0 = the reference's behaviour
 };
 
 #define RT_STACK_DEPTH 96   // traversal stack entries (traverse.cuh); Karras trees are bounded by key + index bits, PLOC trees are checked at build

@@ -55,16 +55,22 @@ __device__ __forceinline__ Ray to_object_space(const SceneView& sv, uint32_t cha
 }
 
 // ---- t-only intersection in object space: returns true and t when the reference's ::hit would accept ----
-__device__ __forceinline__ bool sphere_t(float3 center, float radius, const Ray& r, float t_min, float t_max, float& t) {
-    // sphere.h:38-55 — near root only (the "second root" repeats the first)
+__device__ __forceinline__ bool sphere_t(float3 center, float radius, const Ray& r, float t_min, float t_max, bool far_root, float& t) {
+    // sphere.h:38-55 — near root only (the reference's "second root" repeats the first);
+    // far_root (RT_SEM_SPHERE_FAR_ROOT): the book's second root when the near one is out of range
     const float3 oc = r.o - center;
     const float a = len2(r.d);
     const float half_b = dot3(oc, r.d);
     const float c = len2(oc) - radius * radius;
     const float discriminant = half_b * half_b - a * c;
     if (discriminant < 0) return false;
-    const float root = (-half_b - sqrtf(discriminant)) / a;
-    if (root < t_min || t_max < root) return false;
+    const float sqrtd = sqrtf(discriminant);
+    float root = (-half_b - sqrtd) / a;
+    if (root < t_min || t_max < root) {
+        if (!far_root) return false;
+        root = (-half_b + sqrtd) / a;
+        if (root < t_min || t_max < root) return false;
+    }
     t = root;
     return true;
 }
@@ -111,14 +117,14 @@ __device__ __forceinline__ bool triangle_t(const DPrim& p, const Ray& r, float t
 }
 
 // object-space test of one primitive (ray already in the primitive's frame)
-__device__ __forceinline__ bool prim_t_local(const DPrim& p, const Ray& r, float t_min, float t_max, float& t) {
+__device__ __forceinline__ bool prim_t_local(const DPrim& p, const Ray& r, float t_min, float t_max, uint32_t semantics, float& t) {
     const uint32_t type = prim_type(p);
     if (type <= RT_PRIM_MOVING_SPHERE) {   // one copy of the sphere test for both kinds: only centre and radius differ
         static_assert(RT_PRIM_SPHERE == 0 && RT_PRIM_MOVING_SPHERE == 1, "sphere kinds first");
         float3 center = f3(p.a.x, p.a.y, p.a.z);
         float radius = p.a.w;
         if (type == RT_PRIM_MOVING_SPHERE) { center = moving_center(p, r.tm); radius = p.c0; }
-        return sphere_t(center, radius, r, t_min, t_max, t);
+        return sphere_t(center, radius, r, t_min, t_max, (semantics & RT_SEM_SPHERE_FAR_ROOT) != 0, t);
     }
     if (type == RT_PRIM_TRIANGLE) return triangle_t(p, r, t_min, t_max, t);
     return rect_t(type, p, r, t_min, t_max, t);
@@ -127,7 +133,7 @@ __device__ __forceinline__ bool prim_t_local(const DPrim& p, const Ray& r, float
 // world-space test (applies the primitive's wrapper chain)
 __device__ __forceinline__ bool prim_t(const SceneView& sv, const DPrim& p, const Ray& world, float t_min, float t_max, float& t) {
     const Ray r = to_object_space(sv, prim_chain(p), world);
-    return prim_t_local(p, r, t_min, t_max, t);
+    return prim_t_local(p, r, t_min, t_max, sv.semantics, t);
 }
 
 // ---- hit attributes of the accepted hit: what the reference leaves in hit_record ---------------------
@@ -167,13 +173,12 @@ __device__ __forceinline__ void prim_attr_local(const SceneView& sv, const DPrim
         const float B2 = 1.0f - B0 - B1;
         h.u = B2 * at.uv[0] + B0 * at.uv[2] + B1 * at.uv[4];               // barycentric_interp, triangle.h:113-116
         h.v = B2 * at.uv[1] + B0 * at.uv[3] + B1 * at.uv[5];
-        if (!at.vertex_normals) {
-            set_face_normal(h, r.d, cross3(e1, e0));                       // not normalised
-        } else {
-            const float3 n = f3(B2 * at.n[0] + B0 * at.n[3] + B1 * at.n[6], B2 * at.n[1] + B0 * at.n[4] + B1 * at.n[7],
-                                B2 * at.n[2] + B0 * at.n[5] + B1 * at.n[8]);
-            set_face_normal(h, r.d, n);
-        }
+        float3 n;
+        if (!at.vertex_normals) n = cross3(e1, e0);                        // not normalised
+        else n = f3(B2 * at.n[0] + B0 * at.n[3] + B1 * at.n[6], B2 * at.n[1] + B0 * at.n[4] + B1 * at.n[7],
+                    B2 * at.n[2] + B0 * at.n[5] + B1 * at.n[8]);
+        if (sv.semantics & RT_SEM_UNIT_TRIANGLE_NORMALS) n = unit3(n);
+        set_face_normal(h, r.d, n);
     } else {
         float a, b;
         float3 outward_normal;
@@ -241,7 +246,7 @@ __device__ __forceinline__ bool boundary_t(const SceneView& sv, const DMedium& m
         const uint32_t chain = prim_chain(p);
         if (chain != cc.chain) { cc.ray = to_object_space(sv, chain, r); cc.chain = chain; }
         float tt;
-        if (prim_t_local(p, cc.ray, t_min, closest, tt)) { any = true; closest = tt; }
+        if (prim_t_local(p, cc.ray, t_min, closest, sv.semantics, tt)) { any = true; closest = tt; }
     }
     t = closest;
     return any;

@@ -58,6 +58,64 @@ int rt_average_frames(const uint8_t* frames, int n_frames, int width, int height
     return RT_OK;
 }
 
+// ---- checkpoints ---------------------------------------------------------------------------------------------------
+namespace {
+struct CheckpointHeader {            // 64 bytes, little-endian
+    char magic[8];                   // "RTB2CKPT"
+    uint32_t version, width, height, seed, max_depth, samples_done;
+    uint64_t scene_hash;
+    uint64_t payload_hash;           // FNV-1a of the float payload
+    uint64_t reserved[2];
+};
+static_assert(sizeof(CheckpointHeader) == 64, "checkpoint header layout");
+uint64_t fnv1a(const void* p, size_t n) {
+    uint64_t h = 1469598103934665603ull;
+    const uint8_t* b = static_cast<const uint8_t*>(p);
+    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+    return h;
+}
+} // namespace
+
+int rt_checkpoint_save(const char* path, const rt_checkpoint_info* info, const float* sums) {
+    if (!path || !info || !sums || info->width == 0 || info->height == 0) return fail(RT_ERR_INVALID, "checkpoint_save: bad argument");
+    const size_t n = (size_t)info->width * info->height * 3;
+    CheckpointHeader h{};
+    std::memcpy(h.magic, "RTB2CKPT", 8);
+    h.version = 1; h.width = info->width; h.height = info->height; h.seed = info->seed; h.max_depth = info->max_depth;
+    h.samples_done = info->samples_done; h.scene_hash = info->scene_hash;
+    h.payload_hash = fnv1a(sums, n * sizeof(float));
+    // written next to the target and renamed, so an interrupted save never leaves a truncated checkpoint behind
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE* f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return fail(RT_ERR_INVALID, "checkpoint_save: cannot open " + tmp);
+    const bool ok = std::fwrite(&h, sizeof(h), 1, f) == 1 && std::fwrite(sums, sizeof(float), n, f) == n;
+    if (std::fclose(f) != 0 || !ok) { std::remove(tmp.c_str()); return fail(RT_ERR_INVALID, "checkpoint_save: write failed: " + tmp); }
+    if (std::rename(tmp.c_str(), path) != 0) { std::remove(tmp.c_str()); return fail(RT_ERR_INVALID, std::string("checkpoint_save: cannot rename to ") + path); }
+    return RT_OK;
+}
+
+int rt_checkpoint_load(const char* path, rt_checkpoint_info* info, float* sums, size_t capacity_floats) {
+    if (!path || !info) return fail(RT_ERR_INVALID, "checkpoint_load: bad argument");
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return fail(RT_ERR_INVALID, std::string("checkpoint_load: cannot open ") + path);
+    CheckpointHeader h{};
+    if (std::fread(&h, sizeof(h), 1, f) != 1 || std::memcmp(h.magic, "RTB2CKPT", 8) != 0 || h.version != 1 || h.width == 0 || h.height == 0) {
+        std::fclose(f);
+        return fail(RT_ERR_INVALID, std::string("checkpoint_load: not a checkpoint: ") + path);
+    }
+    std::memset(info, 0, sizeof(*info));
+    info->width = h.width; info->height = h.height; info->seed = h.seed; info->max_depth = h.max_depth;
+    info->samples_done = h.samples_done; info->scene_hash = h.scene_hash;
+    if (sums) {
+        const size_t n = (size_t)h.width * h.height * 3;
+        if (capacity_floats < n) { std::fclose(f); return fail(RT_ERR_INVALID, "checkpoint_load: buffer too small"); }
+        const bool ok = std::fread(sums, sizeof(float), n, f) == n;
+        if (!ok || fnv1a(sums, n * sizeof(float)) != h.payload_hash) { std::fclose(f); return fail(RT_ERR_INVALID, std::string("checkpoint_load: truncated or corrupt: ") + path); }
+    }
+    std::fclose(f);
+    return RT_OK;
+}
+
 int rt_write_ppm(const char* path, const uint8_t* rgb8, int width, int height) {
     if (!path || !rgb8 || width <= 0 || height <= 0) return fail(RT_ERR_INVALID, "write_ppm: bad argument");
     FILE* f = fopen(path, "w");

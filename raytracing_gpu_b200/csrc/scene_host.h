@@ -54,6 +54,7 @@ struct HostScene {
     float background[3] = {0, 0, 0};
     rt_flat_camera camera{};
     bool has_camera = false;
+    uint32_t semantics = 0;   // rt_semantics bits; device-side only (not part of the exported blob)
     FlatScene flat;
 
     // returns number of leaf ids, or a negative rt_status with `err` set

@@ -99,7 +99,7 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
                     if (chain != cached_chain) { cached = to_object_space(sv, chain, ray); cached_chain = chain; }
                     if (COUNT) cnt->prim_tests++;
                     float t;
-                    if (prim_t_local(p, chain ? cached : ray, t_min, best.t, t)) consider(sv, prim, t, best);
+                    if (prim_t_local(p, chain ? cached : ray, t_min, best.t, sv.semantics, t)) consider(sv, prim, t, best);
                 }
                 if (blocked) { parked = node; node = pop(); }
                 if (!__any_sync(0xffffffffu, node != RT_NODE_DONE || parked != RT_NODE_DONE)) break;
@@ -136,7 +136,7 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
             if (chain != cached_chain) { cached = to_object_space(sv, chain, ray); cached_chain = chain; }
             if (COUNT) cnt->prim_tests++;
             float t;
-            if (prim_t_local(p, chain ? cached : ray, t_min, best.t, t)) consider(sv, prim, t, best);
+            if (prim_t_local(p, chain ? cached : ray, t_min, best.t, sv.semantics, t)) consider(sv, prim, t, best);
         }
         node = sp ? stack[--sp] : RT_NODE_DONE;
     }
@@ -235,7 +235,7 @@ __device__ __forceinline__ void closest_surface_stream(const SceneView& sv, floa
             }
             if (COUNT) cnt->prim_tests++;
             float t;
-            if (prim_t_local(p, r, t_min, best.t, t)) consider(sv, prim, t, best);
+            if (prim_t_local(p, r, t_min, best.t, sv.semantics, t)) consider(sv, prim, t, best);
         }
         if (blocked) { parked = node; node = pop(); }
         const bool fin = node == RT_NODE_DONE && parked == RT_NODE_DONE;

@@ -640,11 +640,15 @@ extern "C" int rt_render(rt_scene* s, const rt_render_settings* st, float* out_r
     const size_t n = (size_t)st->width * st->height * 3;
     float* d_accum = nullptr;
     RT_CUDA(cudaMalloc(&d_accum, sizeof(float) * n));
-    RT_CUDA(cudaMemsetAsync(d_accum, 0, sizeof(float) * n, 0));
+    const bool accumulate = (st->flags & RT_RENDER_ACCUMULATE) != 0;   // progressive: out_rgb carries the sums so far
+    if (accumulate) RT_CUDA(cudaMemcpyAsync(d_accum, out_rgb, sizeof(float) * n, cudaMemcpyHostToDevice, 0));
+    else RT_CUDA(cudaMemsetAsync(d_accum, 0, sizeof(float) * n, 0));
     const int rc = render_impl(*ds, *st, d_accum, 0, stats);
     if (rc < 0) { cudaFree(d_accum); return rc; }
-    const uint32_t s_count = st->sample_count ? st->sample_count : st->samples_per_pixel - std::min(st->samples_per_pixel, st->sample_first);
-    k_scale<<<(unsigned)((n + 255) / 256), 256>>>(d_accum, d_accum, n, 1 / (float)s_count);
+    if (!accumulate) {
+        const uint32_t s_count = st->sample_count ? st->sample_count : st->samples_per_pixel - std::min(st->samples_per_pixel, st->sample_first);
+        k_scale<<<(unsigned)((n + 255) / 256), 256>>>(d_accum, d_accum, n, 1 / (float)s_count);
+    }
     RT_CUDA(cudaMemcpy(out_rgb, d_accum, sizeof(float) * n, cudaMemcpyDeviceToHost));
     cudaFree(d_accum);
     return RT_OK;
