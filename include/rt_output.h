@@ -27,6 +27,10 @@ int rt_write_ppm(const char* path, const uint8_t* rgb8, int width, int height);
  * (stored deflate blocks), no libpng / zlib dependency. */
 int rt_write_png(const char* path, const uint8_t* rgb8, int width, int height);
 
+/* Linear float frame as a NumPy .npy file (version 1.0, little-endian float32, shape (height, width, 3), C order; row 0 =
+ * bottom as rt_render returns it): the lossless dump parity work compares, next to the 8-bit files above. */
+int rt_write_npy(const char* path, const float* rgb_linear, int width, int height);
+
 /* ---- progressive rendering checkpoints -------------------------------------------------------------
  * A checkpoint is the accumulation buffer of rt_render(..., RT_RENDER_ACCUMULATE) plus what is needed to continue it:
  * which scene (rt_scene_hash), frame size, seed, depth and how many samples per pixel the sums hold.  Resuming = load,

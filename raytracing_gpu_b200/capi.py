@@ -113,7 +113,7 @@ def lib():
         "rt_obj_add_to_scene": (i32, [vp, vp, i32]),
         # include/rt_output.h
         "rt_average_frames": (i32, [vp, i32, i32, i32, vp]), "rt_write_ppm": (i32, [C.c_char_p, vp, i32, i32]),
-        "rt_write_png": (i32, [C.c_char_p, vp, i32, i32]),
+        "rt_write_png": (i32, [C.c_char_p, vp, i32, i32]), "rt_write_npy": (i32, [C.c_char_p, vp, i32, i32]),
         "rt_draw": (i32, [vp, C.POINTER(DrawSettings), C.c_char_p, vp, C.POINTER(C.c_uint32), C.POINTER(RenderStats)]),
         "rt_checkpoint_save": (i32, [C.c_char_p, C.POINTER(CheckpointInfo), vp]),
         "rt_checkpoint_load": (i32, [C.c_char_p, C.POINTER(CheckpointInfo), vp, C.c_size_t]),
@@ -164,6 +164,11 @@ def write_ppm(path, rgb8):
 def write_png(path, rgb8):
     px = np.ascontiguousarray(rgb8, dtype=np.uint8)
     _check(lib().rt_write_png(os.fsencode(path), px.ctypes.data, px.shape[1], px.shape[0]))
+
+
+def write_npy(path, rgb_linear):
+    px = np.ascontiguousarray(rgb_linear, dtype=np.float32)
+    _check(lib().rt_write_npy(os.fsencode(path), px.ctypes.data, px.shape[1], px.shape[0]))
 
 
 def _check(rc):

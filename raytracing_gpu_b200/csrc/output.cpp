@@ -58,6 +58,20 @@ int rt_average_frames(const uint8_t* frames, int n_frames, int width, int height
     return RT_OK;
 }
 
+int rt_write_npy(const char* path, const float* rgb, int width, int height) {
+    if (!path || !rgb || width <= 0 || height <= 0) return fail(RT_ERR_INVALID, "write_npy: bad argument");
+    std::string dict = "{'descr': '<f4', 'fortran_order': False, 'shape': (" + std::to_string(height) + ", " + std::to_string(width) + ", 3), }";
+    while ((10 + dict.size() + 1) % 64 != 0) dict += ' ';   // magic 6 + version 2 + length 2 + dict + newline: data starts 64-byte aligned
+    dict += '\n';
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(RT_ERR_INVALID, std::string("write_npy: cannot open ") + path);
+    const uint8_t head[10] = {0x93, 'N', 'U', 'M', 'P', 'Y', 1, 0, (uint8_t)(dict.size() & 0xff), (uint8_t)(dict.size() >> 8)};
+    const size_t n = (size_t)width * height * 3;
+    const bool ok = std::fwrite(head, 1, 10, f) == 10 && std::fwrite(dict.data(), 1, dict.size(), f) == dict.size() && std::fwrite(rgb, sizeof(float), n, f) == n;
+    if (std::fclose(f) != 0 || !ok) return fail(RT_ERR_INVALID, std::string("write_npy: write failed: ") + path);
+    return RT_OK;
+}
+
 // ---- checkpoints ---------------------------------------------------------------------------------------------------
 namespace {
 struct CheckpointHeader {            // 64 bytes, little-endian

@@ -98,3 +98,15 @@ def test_bad_arguments():
     sc = rt.Scene()
     with pytest.raises(rt.RtError):
         sc.draw(0, 0.0, 1, 1, image_height=0)               # neither a height nor an aspect ratio
+
+
+def test_write_npy_is_read_back_by_numpy(tmp_path):
+    rng = np.random.default_rng(8)
+    for w, h in ((1, 1), (7, 5), (33, 2)):
+        img = rng.random((h, w, 3), dtype=np.float32) * 3 - 1
+        path = str(tmp_path / f"f_{w}x{h}.npy")
+        rt.write_npy(path, img)
+        back = np.load(path)
+        assert back.dtype == np.float32 and back.shape == (h, w, 3) and (back == img).all()
+    with pytest.raises(rt.RtError, match="cannot open"):
+        rt.write_npy(str(tmp_path / "no_such_dir" / "x.npy"), img)
