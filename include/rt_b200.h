@@ -119,6 +119,8 @@ int rt_scene_hash(rt_scene* s, uint64_t* out);
 int rt_image_height(int width, float aspect);
 
 /* ---- device side ---- */
+enum rt_builder { RT_BUILDER_KARRAS = 0, RT_BUILDER_PLOC = 1, RT_BUILDER_HOST_SAH = 2 };
+
 typedef struct rt_build_stats {
     uint32_t n_prims, n_nodes;
     float ms_upload, ms_morton, ms_sort, ms_hierarchy, ms_refit, ms_collapse, ms_total;
@@ -126,7 +128,8 @@ typedef struct rt_build_stats {
     uint32_t build_rounds;   /* PLOC builds: clustering rounds */
     float sah_internal;      /* PLOC builds: sum of internal-node surface areas / root area */
     uint32_t ploc_radius;    /* PLOC builds: neighbour search radius of the tree that was kept */
-    uint32_t reserved[4];
+    uint32_t builder;        /* rt_builder: which hierarchy builder produced the tree */
+    uint32_t reserved[3];
 } rt_build_stats;
 
 /* Flatten (if needed), upload to `device` and build the LBVH there.  Replaces the one-thread device

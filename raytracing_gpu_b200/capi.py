@@ -35,7 +35,8 @@ class BuildStats(C.Structure):
     _fields_ = [("n_prims", C.c_uint32), ("n_nodes", C.c_uint32), ("ms_upload", C.c_float), ("ms_morton", C.c_float),
                 ("ms_sort", C.c_float), ("ms_hierarchy", C.c_float), ("ms_refit", C.c_float),
                 ("ms_collapse", C.c_float), ("ms_total", C.c_float), ("bvh_depth", C.c_uint32), ("build_rounds", C.c_uint32),
-                ("sah_internal", C.c_float), ("ploc_radius", C.c_uint32), ("reserved", C.c_uint32 * 4)]
+                ("sah_internal", C.c_float), ("ploc_radius", C.c_uint32), ("builder", C.c_uint32),
+                ("reserved", C.c_uint32 * 3)]
 
 
 class CatalogParams(C.Structure):
