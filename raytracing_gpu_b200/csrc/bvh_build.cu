@@ -73,7 +73,28 @@ __device__ Box local_box(const DPrim& p, float t_lo, float t_hi) {
 __device__ Box world_box(const SceneView& sv, const DPrim& p, float t_lo, float t_hi) {
     Box b = local_box(p, t_lo, t_hi);
     const uint32_t chain = p.type_chain >> 4;
-    if (chain) {
+    const uint32_t type = p.type_chain & 15u;
+    if (chain && type <= RT_PRIM_MOVING_SPHERE) {
+        // a rotated sphere is a sphere: move the CENTRE(S) through the chain and keep the radius, instead of bounding the
+        // rotated bounding cube (22 % wider in x and z at the 15 degrees of the final scene's 1000-sphere instance)
+        const float r = fabsf(type == RT_PRIM_SPHERE ? p.a.w : p.c0);
+        const rt_flat_chain c = sv.chains[chain];
+        b = empty_box();
+        const int n_centres = type == RT_PRIM_SPHERE ? 1 : 2;
+        for (int k = 0; k < n_centres; k++) {
+            float cx = p.a.x, cy = p.a.y, cz = p.a.z;
+            if (type == RT_PRIM_MOVING_SPHERE) {
+                const float w = ((k ? t_hi : t_lo) - p.b.z) / (p.b.w - p.b.z);
+                cx = p.a.x + w * (p.a.w - p.a.x); cy = p.a.y + w * (p.b.x - p.a.y); cz = p.a.z + w * (p.b.y - p.a.z);
+            }
+            for (int j = (int)c.count - 1; j >= 0; j--) {
+                const rt_flat_xop op = sv.xops[c.first + j];
+                if (op.kind == RT_XOP_TRANSLATE) { cx += op.a; cy += op.b; cz += op.c; }
+                else { const float x = op.b * cx + op.a * cz, z = -op.a * cx + op.b * cz; cx = x; cz = z; }   // hittable.h:131-132
+            }
+            grow(b, cx - r, cy - r, cz - r); grow(b, cx + r, cy + r, cz + r);
+        }
+    } else if (chain) {
         const rt_flat_chain c = sv.chains[chain];
         for (int k = (int)c.count - 1; k >= 0; k--) {
             const rt_flat_xop op = sv.xops[c.first + k];
