@@ -142,6 +142,76 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     }
 }
 
+// Suspendable walk (k_extend_pass): closest_surface<PARKED = true> whose traversal state is the caller's, so a walk can
+// be cut short and taken up again by another warp.  Rays of one 32-ray batch finish at very different times (only ~60 %
+// of the node steps a warp pays for carry a live lane on the final scene); instead of letting the last few lanes run the
+// warp alone, the walk stops once no more than `suspend_below` lanes are still live (checked where the warp leaves the
+// node loop anyway: the leaf phase), the caller stores those lanes' state, and a later pass packs 32 such stragglers
+// into one warp.  A lane is live while it has a node to visit or a leaf parked.  The closest hit of a ray depends
+// neither on where its walk is cut nor on its neighbours: the state is the complete traversal state.
+// WARP-COLLECTIVE; lanes without a ray enter with node = parked = RT_NODE_DONE.  A warp does not suspend while some lane's
+// stack is deeper than RT_SUSPEND_STACK (what a continuation record holds).
+#define RT_SUSPEND_STACK 24
+struct Walk { int node, parked, sp; };
+
+template <bool COUNT>
+__device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray& ray, float t_min, Closest& best, TraversalCounters* cnt,
+                                                 Walk& w, int* stack, uint32_t suspend_below, uint32_t* steps) {
+    const float tiny = 1e-20f;
+    const float ix = 1.0f / (fabsf(ray.d.x) < tiny ? copysignf(tiny, ray.d.x) : ray.d.x);
+    const float iy = 1.0f / (fabsf(ray.d.y) < tiny ? copysignf(tiny, ray.d.y) : ray.d.y);
+    const float iz = 1.0f / (fabsf(ray.d.z) < tiny ? copysignf(tiny, ray.d.z) : ray.d.z);
+    const float ox = ray.o.x * ix, oy = ray.o.y * iy, oz = ray.o.z * iz;
+    uint32_t cached_chain = 0;
+    Ray cached = ray;
+    int node = w.node, parked = w.parked, sp = w.sp;
+    auto pop = [&]() { return sp ? stack[--sp] : RT_NODE_DONE; };
+    for (;;) {
+        if (node >= 0) {
+            const BNode* np = sv.nodes + node;
+            const float4 n0 = __ldg(&np->n0), n1 = __ldg(&np->n1), n2 = __ldg(&np->n2);
+            const int2 ch = __ldg(reinterpret_cast<const int2*>(&np->child0));
+            if (COUNT) cnt->nodes++;
+            const float c0lox = fmaf(n0.x, ix, -ox), c0hix = fmaf(n0.y, ix, -ox), c0loy = fmaf(n0.z, iy, -oy), c0hiy = fmaf(n0.w, iy, -oy);
+            const float c1lox = fmaf(n1.x, ix, -ox), c1hix = fmaf(n1.y, ix, -ox), c1loy = fmaf(n1.z, iy, -oy), c1hiy = fmaf(n1.w, iy, -oy);
+            const float c0loz = fmaf(n2.x, iz, -oz), c0hiz = fmaf(n2.y, iz, -oz), c1loz = fmaf(n2.z, iz, -oz), c1hiz = fmaf(n2.w, iz, -oz);
+            const float t0n = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
+            const float t0f = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
+            const float t1n = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
+            const float t1f = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), best.t));
+            const bool h0 = t0n <= t0f, h1 = t1n <= t1f;
+            if (h0 && h1) {
+                const bool swap = t1n < t0n;
+                stack[sp++] = swap ? ch.x : ch.y;
+                node = swap ? ch.y : ch.x;
+            } else if (h0) node = ch.x;
+            else if (h1) node = ch.y;
+            else node = pop();
+            if (node < 0 && node != RT_NODE_DONE && parked == RT_NODE_DONE) { parked = node; node = pop(); }
+        }
+        const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
+        const bool any_blocked = __any_sync(0xffffffffu, blocked), any_walking = __any_sync(0xffffffffu, node >= 0);
+        if (COUNT) (*steps)++;
+        if (any_blocked || !any_walking) {
+            if (parked != RT_NODE_DONE) {
+                const int prim = ~parked;
+                parked = RT_NODE_DONE;
+                const DPrim p = sv.prims[prim];
+                const uint32_t chain = prim_chain(p);
+                if (chain != cached_chain) { cached = to_object_space(sv, chain, ray); cached_chain = chain; }
+                if (COUNT) cnt->prim_tests++;
+                float t;
+                if (prim_t_local(p, chain ? cached : ray, t_min, best.t, sv.semantics, t)) consider(sv, prim, t, best);
+            }
+            if (blocked) { parked = node; node = pop(); }
+            const uint32_t live = __ballot_sync(0xffffffffu, node != RT_NODE_DONE || parked != RT_NODE_DONE);
+            if (!live) break;
+            if ((uint32_t)__popc(live) <= suspend_below && !__any_sync(0xffffffffu, sp > RT_SUSPEND_STACK)) break;
+        }
+    }
+    w.node = node; w.parked = parked; w.sp = sp;
+}
+
 // Streaming closest-hit for a persistent warp (k_extend): rays of one warp finish at very different times — measured on
 // the final scene, only 59 % of the node steps a warp pays for carry a live lane (rt_render_stats::node_slots) — so a
 // lane that has finished does not wait for the slowest ray of its batch: once fewer than REFILL_BELOW lanes still walk

@@ -25,6 +25,8 @@
 
 #include <cuda_pipeline.h>
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -34,6 +36,7 @@ constexpr int NQ = 6;                 // material classes: 0 = miss, 1 + rt_mate
 constexpr int Q_MISS = 0;
 constexpr int POLL_DEPTH = 4;         // host runs this many iterations ahead of the counter it polls
 constexpr int POLL_SLOTS = 8;
+constexpr int Q_SUSP = NQ;            // deferred extend: the walk of this path is suspended and the path has moved into its continuation record
 
 // every hot counter on its own 128-byte line (its own L2 slice): same-line atomics serialise
 struct __align__(128) Counters {
@@ -44,6 +47,9 @@ struct __align__(128) Counters {
     unsigned long long next_sample;   unsigned long long pad4[15];   // global sample cursor (sample-major: g = sample * npix + pixel)
     unsigned long long total_rays, nodes, prim_tests, node_slots;
     unsigned long long iter_begin;    // min(next_sample, total) when the current iteration started (written by generate / turnover only)
+    unsigned long long pad5[11];
+    struct { uint32_t n, pad[31]; } cont[2];      // continuation records in list b (written by the extend of iterations with cur = b)
+    struct { uint32_t n, pad[31]; } n_fin[2];     // resumed paths that finished their walk in this iteration: region [capacity, capacity + n) of pool b
 };
 
 struct PoolView {
@@ -52,6 +58,14 @@ struct PoolView {
     float4* thr[2];      // throughput rgb, bits: pixel
     uint2* hit;          // written by extend: bits of t, Closest::prim
     uint8_t* hit_class;  // written by extend: material class of the hit
+    // continuation records of suspended walks (k_extend_defer), two lists: extend(cur) reads list cur ^ 1 and writes list cur.
+    // A record owns its path: the pool slot it came from is a hole (class Q_SUSP) that shade skips.
+    uint4* cont_walk[2];   // bits of the closest t so far, its primitive, node, parked leaf
+    float4* cont_o[2];     // the path: ray origin + time,
+    float4* cont_d[2];     //   direction + sample / bounce word,
+    float4* cont_thr[2];   //   throughput + pixel
+    uint8_t* cont_sp[2];   // stack entries
+    int* cont_stack[2];    // [entry * capacity + record]
     Counters* c;
     uint32_t capacity;
 };
@@ -64,13 +78,25 @@ struct RenderPool {
     cudaEvent_t poll_ev[POLL_SLOTS]{};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     int grid_extend = 0, grid_shade = 0, shade_block = 256;
+    RenderPool* second = nullptr;        // two-lane rendering: the second lane's pools (owned)
+    cudaStream_t own_stream = nullptr;   //   and its stream
+    cudaEvent_t ev_extend = nullptr;     //   recorded after each extend launch of this lane
+    int lanes = 1;
+    uint32_t suspend_below = 0;          // deferred extend (k_extend_defer): a full warp suspends once <= this many lanes are live; 0 = k_extend
     std::vector<cudaEvent_t> timer_ev;   // RT_RENDER_TIMERS: 3 events per iteration, reused across frames
 };
 
 void render_pool_destroy(RenderPool* p) {
     if (!p) return;
+    render_pool_destroy(p->second);
+    if (p->own_stream) cudaStreamDestroy(p->own_stream);
+    if (p->ev_extend) cudaEventDestroy(p->ev_extend);
     for (int b = 0; b < 2; b++) { cudaFree(p->v.ray_o[b]); cudaFree(p->v.ray_d[b]); cudaFree(p->v.thr[b]); }
     cudaFree(p->v.hit); cudaFree(p->v.hit_class); cudaFree(p->v.c);
+    for (int b = 0; b < 2; b++) {
+        cudaFree(p->v.cont_walk[b]); cudaFree(p->v.cont_o[b]); cudaFree(p->v.cont_d[b]); cudaFree(p->v.cont_thr[b]);
+        cudaFree(p->v.cont_sp[b]); cudaFree(p->v.cont_stack[b]);
+    }
     if (p->h_live) cudaFreeHost(p->h_live);
     if (p->h_counters) cudaFreeHost(p->h_counters);
     for (auto& e : p->poll_ev) if (e) cudaEventDestroy(e);
@@ -93,6 +119,7 @@ struct FrameParams {
 };
 
 constexpr int EXTEND_BLOCK = 128;
+constexpr uint32_t SUSPEND_MIN_PRIMS = 65536, SUSPEND_BELOW_DEFAULT = 8;
 #ifndef EXTEND_MIN_BLOCKS
 #define EXTEND_MIN_BLOCKS 8
 #endif
@@ -211,6 +238,101 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
     }
 }
 
+// Deferred extend (walk_suspendable): a warp stops walking once no more than `suspend_below` of its 32 rays are still
+// live and moves those paths — ray, throughput, traversal state — into a continuation list; their pool slots become holes
+// (class Q_SUSP) that shade skips.  The NEXT iteration's extend takes the suspended walks up again, 32 stragglers to a
+// warp, before it starts on the pool (longest work first); a resumed path that finishes its walk is written, with its hit
+// record, to the region [capacity, capacity + n_fin) of the current pool, which shade treats like any other path.  A
+// suspended path simply bounces an iteration later.  Nothing waits for stragglers: a second pass inside the same
+// iteration raised the lane utilisation of the node loop just as much but paid for it with the latency of the longest
+// walks at the end of every iteration (profiles/r01_v9_experiments.md).
+template <bool COUNT>
+__global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend_defer(SceneView sv, PoolView pv, FrameParams fp, int cur, uint32_t suspend_below) {
+    const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
+    const int rd = cur ^ 1, wr = cur;
+    const uint32_t n_c = pv.c->cont[rd].n, n_c32 = (n_c + 31u) & ~31u;   // work index space: continuation records (padded to whole warps), then the pool
+    const uint32_t n = n_c32 + n_pool;
+    const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    TraversalCounters tc{0, 0};
+    uint32_t steps = 0;
+    int stack[RT_STACK];
+    for (;;) {
+        const uint32_t base = warp_claim(&pv.c->cur_extend);
+        if (base >= n) break;
+        const bool resumed = base < n_c32;                       // warp-uniform
+        const uint32_t idx = (resumed ? base : base - n_c32) + lane;
+        const bool active = idx < (resumed ? n_c : n_pool);
+        Walk w{RT_NODE_DONE, RT_NODE_DONE, 0};
+        Closest c; c.t = INFINITY; c.prim = -1;
+        uint32_t pos = 0;
+        float4 o, d, th = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (resumed) {
+            const uint32_t rec = active ? idx : base;
+            o = pv.cont_o[rd][rec]; d = pv.cont_d[rd][rec];
+            if (active) {
+                const uint4 ws = pv.cont_walk[rd][idx];
+                th = pv.cont_thr[rd][idx];
+                c.t = __uint_as_float(ws.x); c.prim = (int)ws.y; w.node = (int)ws.z; w.parked = (int)ws.w;
+                w.sp = (int)pv.cont_sp[rd][idx];
+                for (int k = 0; k < w.sp; k++) stack[k] = pv.cont_stack[rd][(size_t)k * pv.capacity + idx];
+            }
+        } else {
+            pos = pos_of(active ? idx : idx - lane, n_b, n_pool, pv.capacity);
+            o = pv.ray_o[cur][pos]; d = pv.ray_d[cur][pos];
+            if (active && sv.n_prims) w.node = 0;
+        }
+        Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
+        // only whole batches suspend: a few stragglers left over at the end of a list would otherwise advance a leaf phase per iteration
+        const uint32_t below = __all_sync(0xffffffffu, active) ? suspend_below : 0u;
+        walk_suspendable<COUNT>(sv, r, 0.001f, c, &tc, w, stack, below, &steps);                                    // render.h:63
+        const bool suspended = w.node != RT_NODE_DONE || w.parked != RT_NODE_DONE;
+        const uint32_t ms = __ballot_sync(0xffffffffu, suspended);
+        if (ms) {
+            uint32_t slot = 0;
+            if (lane == (uint32_t)(__ffs(ms) - 1)) slot = atomicAdd(&pv.c->cont[wr].n, (uint32_t)__popc(ms));
+            slot = __shfl_sync(0xffffffffu, slot, __ffs(ms) - 1) + __popc(ms & lt);
+            if (suspended) {
+                if (!resumed) { th = pv.thr[cur][pos]; pv.hit_class[pos] = (uint8_t)Q_SUSP; }
+                pv.cont_o[wr][slot] = o; pv.cont_d[wr][slot] = d; pv.cont_thr[wr][slot] = th;
+                pv.cont_walk[wr][slot] = make_uint4(__float_as_uint(c.t), (uint32_t)c.prim, (uint32_t)w.node, (uint32_t)w.parked);
+                pv.cont_sp[wr][slot] = (uint8_t)w.sp;
+                for (int k = 0; k < w.sp; k++) pv.cont_stack[wr][(size_t)k * pv.capacity + slot] = stack[k];
+            }
+        }
+        const bool finished = active && !suspended;
+        if (resumed) {   // finished resumed paths re-enter the pool behind its two regions
+            const uint32_t mf = __ballot_sync(0xffffffffu, finished);
+            uint32_t k = 0;
+            if (mf && lane == (uint32_t)(__ffs(mf) - 1)) k = atomicAdd(&pv.c->n_fin[cur].n, (uint32_t)__popc(mf));
+            if (mf) k = __shfl_sync(0xffffffffu, k, __ffs(mf) - 1) + __popc(mf & lt);
+            if (finished) {
+                pos = pv.capacity + k;
+                pv.ray_o[cur][pos] = o; pv.ray_d[cur][pos] = d; pv.thr[cur][pos] = th;
+            }
+        }
+        if (finished) {
+            // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched when a ray really crosses a boundary
+            if (sv.n_active_media) closest_medium(sv, r, 0.001f, c, [&](uint32_t m) {
+                const uint32_t sb = __float_as_uint(d.w);
+                const RngKey key{__float_as_uint(resumed ? th.w : pv.thr[cur][pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
+                return draw4(key, RT_STREAM_MEDIUM, m).x;
+            });
+            int q = Q_MISS;
+            if (c.prim != -1) {
+                const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
+                q = 1 + (int)sv.materials[mat].type;
+            }
+            pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
+            pv.hit_class[pos] = (uint8_t)q;
+        }
+    }
+    if (COUNT) {
+        atomicAdd(&pv.c->nodes, (unsigned long long)tc.nodes);
+        atomicAdd(&pv.c->prim_tests, (unsigned long long)tc.prim_tests);
+        if (lane == 0) atomicAdd(&pv.c->node_slots, 32ull * steps);
+    }
+}
+
 // Streaming variant (closest_surface_stream): finished lanes are refilled from the queue while the rest of the warp
 // keeps walking.  Same results ray by ray; only which lane traces which ray changes.
 // A refill must not cost a round trip to the queue cursor plus one to the pool (both DRAM latencies, paid with most of
@@ -322,10 +444,11 @@ __device__ __forceinline__ void accumulate(float* accum, uint32_t pixel, float3 
     if (c.z != 0.f) atomicAdd(&accum[3 * (size_t)pixel + 2], c.z);
 }
 
-template <int SHADE_BLOCK>
-__global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+template <int SHADE_BLOCK, bool DEFER>
+__device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
     constexpr int SHADE_WARPS = SHADE_BLOCK / 32;
-    constexpr int NC = NQ + 1;                       // + "no path" (tile tail)
+    constexpr int NP = NQ;                           // "no path": the tile tail and (deferred extend) the holes suspended paths leave
+    constexpr int NC = NP + 1;
     __shared__ uint32_t s_tile[2];                   // this tile / the next one (claimed while this one is shaded)
     __shared__ uint32_t s_cnt[64];                   // [class][warp] counts -> exclusive offsets
     __shared__ uint16_t s_perm[SHADE_BLOCK];         // sorted rank -> tile-local index | class << 12
@@ -335,16 +458,19 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
     static_assert(NC * SHADE_WARPS <= 64, "class table must fit one warp scan of two cells per lane");
 
     const int next = cur ^ 1;
-    const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
+    // tile index space: bounced paths, fresh camera paths, (deferred extend) the resumed paths that finished at positions >= capacity
+    const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
+    const uint32_t n = n_pool + (DEFER ? pv.c->n_fin[cur].n : 0u);
     const unsigned long long iter_begin = pv.c->iter_begin;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
+    auto pos_at = [&](uint32_t idx) { return DEFER && idx >= n_pool ? pv.capacity + (idx - n_pool) : pos_of(idx, n_b, n_pool, pv.capacity); };
     if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0;
     if (threadIdx.x == 0) s_tile[0] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
     __syncthreads();
     auto class_of = [&](uint32_t tile) {             // material class of this thread's path in `tile` (NQ past the end)
         const uint32_t idx = tile + threadIdx.x;
-        return idx < n ? (int)pv.hit_class[pos_of(idx, n_b, n, pv.capacity)] : (int)NQ;
+        return idx < n ? min((int)pv.hit_class[pos_at(idx)], NP) : (int)NP;      // Q_SUSP == NP
     };
     uint32_t tile = s_tile[0];
     int cls = class_of(tile);
@@ -380,8 +506,8 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
         // -- shade one path
         bool continues = false, terminated = false;
         float4 new_o, new_d, new_thr;
-        if (k < NQ) {
-            const uint32_t pos = pos_of(tile + (e & 0xfffu), n_b, n, pv.capacity);
+        if (k < NP) {
+            const uint32_t pos = pos_at(tile + (e & 0xfffu));
             const float4 th = pv.thr[cur][pos];
             const float4 d = pv.ray_d[cur][pos];
             const uint32_t pixel = __float_as_uint(th.w), sb = __float_as_uint(d.w);
@@ -465,6 +591,11 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
     }
 }
 
+template <int SHADE_BLOCK>
+__global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_tiles<SHADE_BLOCK, false>(sv, pv, fp, cur); }
+// shade of the deferred extend: holes (Q_SUSP) in the tiles and the finished-resumed region behind the pool; held to the 64 registers the plain kernel gets
+__global__ void __launch_bounds__(256, 4) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_tiles<256, true>(sv, pv, fp, cur); }
+
 // ---- turnover -------------------------------------------------------------------------------------
 __global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out) {
     Counters* c = pv.c;
@@ -474,7 +605,9 @@ __global__ void k_turnover(PoolView pv, int cur, unsigned long long total_sample
     c->n_fresh[cur ^ 1] = (uint32_t)(started - c->iter_begin);
     c->iter_begin = started;
     c->cur_extend = 0; c->cur_shade = 0;
-    *live_out = c->n_bounce[cur ^ 1] + c->n_fresh[cur ^ 1];
+    c->cont[cur ^ 1].n = 0;       // consumed by this iteration's extend; the next iteration's extend appends to it
+    c->n_fin[cur].n = 0;
+    *live_out = c->n_bounce[cur ^ 1] + c->n_fresh[cur ^ 1] + c->cont[cur].n;   // + the suspended paths the next extend resumes
 }
 
 __global__ void k_scale(const float* sums, float* out, size_t n, float scale) {
@@ -482,23 +615,39 @@ __global__ void k_scale(const float* sums, float* out, size_t n, float scale) {
     if (i < n) out[i] = scale * sums[i];      // col / float(ns) = (1/ns) * col, render.h:112 + vec3.h:117
 }
 
-int pool_create(DeviceScene& ds, uint32_t capacity) {
+uint32_t suspend_threshold(const DeviceScene& ds) {
+    if (const char* e = getenv("RT_SUSPEND")) return (uint32_t)std::min(std::max(atoi(e), 0), 31);
+    return ds.view.n_prims >= SUSPEND_MIN_PRIMS ? SUSPEND_BELOW_DEFAULT : 0u;
+}
+
+// `owner`: where the pool is kept (DeviceScene::pool, or RenderPool::second for the second lane); set before the first
+// allocation so that a failure is cleaned up with the scene.
+int pool_create(DeviceScene& ds, RenderPool** owner, uint32_t capacity, int lanes) {
     RenderPool* p = new RenderPool;
     p->device = ds.device;
     p->v.capacity = capacity;
-    ds.pool = p;   // owned from here on: a failed allocation below is cleaned up with the scene
+    p->lanes = lanes;
+    *owner = p;
+    // Deferred extend: a whole warp suspends its stragglers once <= suspend_below lanes are live.  On by default for scenes
+    // whose walks are long and uneven — above SUSPEND_MIN_PRIMS primitives, i.e. triangle meshes: 1 M triangles +7.8 %
+    // (lane utilisation of the node loop 0.42 -> 0.61-0.68, extend -11 %) — and off where the node loop is already
+    // 0.64-0.87 full (every scene the reference ships: the holes suspended paths leave in the shade tiles cost more than
+    // extend gains; profiles/r01_v9_experiments.md).  RT_SUSPEND=n forces a threshold, 0 = off.
+    p->suspend_below = suspend_threshold(ds);
+    const size_t slots = p->suspend_below ? 2 * (size_t)capacity : capacity;   // + the suspended region at positions >= capacity
     for (int b = 0; b < 2; b++) {
-        RT_CUDA(cudaMalloc(&p->v.ray_o[b], sizeof(float4) * capacity));
-        RT_CUDA(cudaMalloc(&p->v.ray_d[b], sizeof(float4) * capacity));
-        RT_CUDA(cudaMalloc(&p->v.thr[b], sizeof(float4) * capacity));
+        RT_CUDA(cudaMalloc(&p->v.ray_o[b], sizeof(float4) * slots));
+        RT_CUDA(cudaMalloc(&p->v.ray_d[b], sizeof(float4) * slots));
+        RT_CUDA(cudaMalloc(&p->v.thr[b], sizeof(float4) * slots));
     }
-    RT_CUDA(cudaMalloc(&p->v.hit, sizeof(uint2) * capacity));
-    RT_CUDA(cudaMalloc(&p->v.hit_class, sizeof(uint8_t) * capacity));
+    RT_CUDA(cudaMalloc(&p->v.hit, sizeof(uint2) * slots));
+    RT_CUDA(cudaMalloc(&p->v.hit_class, sizeof(uint8_t) * slots));
     RT_CUDA(cudaMalloc(&p->v.c, sizeof(Counters)));
     RT_CUDA(cudaHostAlloc(&p->h_live, sizeof(uint32_t) * POLL_SLOTS, cudaHostAllocMapped));
     RT_CUDA(cudaHostAlloc(&p->h_counters, sizeof(Counters), cudaHostAllocDefault));
     for (auto& e : p->poll_ev) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     RT_CUDA(cudaEventCreate(&p->ev_begin)); RT_CUDA(cudaEventCreate(&p->ev_end));
+    RT_CUDA(cudaEventCreateWithFlags(&p->ev_extend, cudaEventDisableTiming));
     int sms = 0;
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
     int occ = 0;
@@ -508,8 +657,47 @@ int pool_create(DeviceScene& ds, uint32_t capacity) {
     if (p->shade_block == 128) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<128>, 128, 0));
     else RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<256>, 256, 0));
     p->grid_shade = sms * std::max(occ, 1);
+    if (p->suspend_below) {
+        for (int b = 0; b < 2; b++) {
+            RT_CUDA(cudaMalloc(&p->v.cont_walk[b], sizeof(uint4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_o[b], sizeof(float4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_d[b], sizeof(float4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_thr[b], sizeof(float4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_sp[b], sizeof(uint8_t) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_stack[b], sizeof(int) * (size_t)capacity * RT_SUSPEND_STACK));
+        }
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend_defer<false>, EXTEND_BLOCK, 0));
+        p->grid_extend = sms * std::max(occ, 1);
+        RT_CUDA((cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_defer, 256, 0)));
+        p->grid_shade = sms * std::max(occ, 1);
+        p->shade_block = 256;
+    }
+    if (lanes > 1) {
+        // two lanes share the SMs: the persistent grids are sized so that one lane's extend and the other lane's shade
+        // are resident together (RT_LANE_GRID="extend blocks per SM,shade blocks per SM")
+        int eb = 6, sb = 1;
+        if (const char* e = getenv("RT_LANE_GRID")) sscanf(e, "%d,%d", &eb, &sb);
+        p->grid_extend = sms * std::max(1, std::min(eb, p->grid_extend / sms));
+        p->grid_shade = sms * std::max(1, std::min(sb, p->grid_shade / sms));
+    }
+    if (const char* e = getenv("RT_GRID_DIV")) {   // experiment: several renders sharing one GPU (tools/overlap_probe.py)
+        const int div = std::max(1, atoi(e));
+        p->grid_extend = std::max(sms, p->grid_extend / div);
+        p->grid_shade = std::max(sms, p->grid_shade / div);
+    }
     return RT_OK;
 }
+
+// One wavefront pipeline of a frame: its pools, its share of the samples, its stream.
+struct LaneRun {
+    RenderPool* P = nullptr;
+    FrameParams fp{};
+    cudaStream_t stream = nullptr;
+    uint32_t* d_live = nullptr;
+    uint64_t it = 0, launches = 0, iterations = 0, max_iterations = 0;
+    size_t n_timer = 0;
+    bool done = false;
+};
 
 int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, cudaStream_t stream, rt_render_stats* stats) {
     if (st.width == 0 || st.height == 0 || st.samples_per_pixel == 0 || st.max_depth == 0 || st.max_depth > 255) {
@@ -532,90 +720,146 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         if (owned && (owned - 1) * tile_count + st.tile_index == nb - 1) npix -= nb * RT_TILE_BLOCK_PIXELS - frame_pix;
     }
     const unsigned long long total = npix * s_count;
+    // Two lanes (RT_LANES=2): the sample range is cut in two and each half runs as its own wavefront pipeline — pools,
+    // counters, stream — into the same accumulation buffer.  The lanes' extend kernels are chained by events so that they
+    // alternate, which leaves one lane's latency-bound shade running beside the other lane's extend.  Which lane traces a
+    // sample does not change it (Philox keys), so the image is the same up to the order of the float atomics.
+    int lanes = getenv("RT_LANES") ? std::min(2, std::max(1, atoi(getenv("RT_LANES")))) : 1;
+    if (s_count < 2 || total < (1ull << 16)) lanes = 1;
     uint32_t capacity = st.pool_paths ? st.pool_paths : (1u << 22);
-    capacity = (uint32_t)std::min<unsigned long long>(capacity, std::max<unsigned long long>(total, 32ull));
+    capacity = (uint32_t)std::min<unsigned long long>(capacity, std::max<unsigned long long>((total + lanes - 1) / lanes, 32ull));
     capacity = (capacity + 31u) & ~31u;
-    if (ds.pool && ds.pool->v.capacity != capacity) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
-    if (!ds.pool) { const int rc = pool_create(ds, capacity); if (rc < 0) return rc; }
-    RenderPool& P = *ds.pool;
+    if (ds.pool && (ds.pool->v.capacity != capacity || ds.pool->lanes != lanes || ds.pool->suspend_below != suspend_threshold(ds))) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
+    if (!ds.pool) {
+        int rc = pool_create(ds, &ds.pool, capacity, lanes);
+        if (rc < 0) return rc;
+        if (lanes > 1) {
+            rc = pool_create(ds, &ds.pool->second, capacity, lanes);
+            if (rc < 0) return rc;
+            RT_CUDA(cudaStreamCreateWithFlags(&ds.pool->second->own_stream, cudaStreamNonBlocking));
+        }
+    }
     const bool count = (st.flags & RT_RENDER_COUNTERS) != 0;
     const bool timers = (st.flags & RT_RENDER_TIMERS) != 0;
-    size_t n_timer = 0;
-    auto tick = [&]() -> int {   // records the next timer event on the stream
+    const uint32_t exp_bits = (uint32_t)(getenv("RT_EXP") ? atoi(getenv("RT_EXP")) : 0);
+
+    LaneRun run[2];
+    uint32_t first = s_first;
+    for (int l = 0; l < lanes; l++) {
+        LaneRun& L = run[l];
+        L.P = l ? ds.pool->second : ds.pool;
+        L.stream = l ? L.P->own_stream : stream;
+        const uint32_t share = lanes == 1 ? s_count : (l == 0 ? (s_count + 1) / 2 : s_count / 2);
+        const unsigned long long lane_total = npix * share;
+        const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
+        L.fp = FrameParams{st.width, st.height, st.max_depth, st.seed, first, exp_bits, lane_total, npix, magic, d_accum, st.tile_index, tile_count};
+        first += share;
+        // hard bound: every iteration with live paths retires >= 1 segment of a path of <= max_depth segments
+        // (deferred extend: a suspended walk advances by at least one leaf phase per iteration, and only whole warps suspend)
+        L.max_iterations = ((lane_total / capacity + 2) * (uint64_t)st.max_depth + POLL_DEPTH + 64) * (L.P->suspend_below ? 64u : 1u);
+        RT_CUDA(cudaHostGetDevicePointer(&L.d_live, L.P->h_live, 0));
+        L.done = lane_total == 0;
+    }
+    auto tick = [&](LaneRun& L) -> int {   // records the lane's next timer event on its stream
         if (!timers) return RT_OK;
-        if (n_timer == P.timer_ev.size()) { cudaEvent_t e; RT_CUDA(cudaEventCreate(&e)); P.timer_ev.push_back(e); }
-        RT_CUDA(cudaEventRecord(P.timer_ev[n_timer++], stream));
+        RenderPool& P = *L.P;
+        if (L.n_timer == P.timer_ev.size()) { cudaEvent_t e; RT_CUDA(cudaEventCreate(&e)); P.timer_ev.push_back(e); }
+        RT_CUDA(cudaEventRecord(P.timer_ev[L.n_timer++], L.stream));
         return RT_OK;
     };
 
-    const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
-    FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, (uint32_t)(getenv("RT_EXP") ? atoi(getenv("RT_EXP")) : 0), total, npix, magic, d_accum, st.tile_index, tile_count};
-    uint64_t launches = 0, iterations = 0;
-    float ms_gen = 0.f;
-    RT_CUDA(cudaMemsetAsync(P.v.c, 0, sizeof(Counters), stream));
-    RT_CUDA(cudaEventRecord(P.ev_begin, stream));
-    if (total > 0) {
+    RenderPool& P0 = *ds.pool;
+    RT_CUDA(cudaEventRecord(P0.ev_begin, stream));
+    for (int l = 0; l < lanes; l++) {
+        LaneRun& L = run[l];
+        if (l) RT_CUDA(cudaStreamWaitEvent(L.stream, P0.ev_begin, 0));   // the caller's stream orders the buffer before this call
+        RT_CUDA(cudaMemsetAsync(L.P->v.c, 0, sizeof(Counters), L.stream));
+        if (L.done) continue;
         // frame start: the first min(capacity, total) samples fill pool 0
-        const uint32_t n0 = (uint32_t)std::min<unsigned long long>(capacity, total);
-        k_generate<<<(n0 + 255) / 256, 256, 0, stream>>>(ds.view, P.v, fp, n0);
-        launches += 1;
-        uint32_t* d_live = nullptr;
-        RT_CUDA(cudaHostGetDevicePointer(&d_live, P.h_live, 0));
-        bool done = false;
-        // hard bound: every iteration with live paths retires >= 1 segment of a path of <= max_depth segments
-        const uint64_t max_iterations = (total / capacity + 2) * (uint64_t)st.max_depth + POLL_DEPTH + 64;
-        for (uint64_t it = 0; !done; it++) {
-            const int cur = (int)(it & 1);
-            if (tick() < 0) return RT_ERR_CUDA;
-            if (fp.pad & 16u) {   // RT_EXP=16: streaming refill
-                if (count) k_extend_stream<true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
-                else k_extend_stream<false><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
-            } else if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
-            else if (fp.pad & 4u) k_extend<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);   // RT_EXP=4: fused loop
-            else k_extend<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, stream>>>(ds.view, P.v, fp, cur);
-            if (tick() < 0) return RT_ERR_CUDA;
-            if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, stream>>>(ds.view, P.v, fp, cur);
-            else k_shade<256><<<P.grid_shade, 256, 0, stream>>>(ds.view, P.v, fp, cur);
-            if (tick() < 0) return RT_ERR_CUDA;
-            k_turnover<<<1, 1, 0, stream>>>(P.v, cur, fp.total_samples, d_live + (it % POLL_SLOTS));
-            RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
-            launches += 3;
-            iterations++;
-            if (it >= POLL_DEPTH) {
-                const uint64_t old = it - POLL_DEPTH;
+        const uint32_t n0 = (uint32_t)std::min<unsigned long long>(capacity, L.fp.total_samples);
+        k_generate<<<(n0 + 255) / 256, 256, 0, L.stream>>>(ds.view, L.P->v, L.fp, n0);
+        L.launches += 1;
+    }
+    for (bool all_done = false; !all_done;) {
+        all_done = true;
+        for (int l = 0; l < lanes; l++) {
+            LaneRun& L = run[l];
+            if (L.done) continue;
+            all_done = false;
+            RenderPool& P = *L.P;
+            const int cur = (int)(L.it & 1);
+            // two lanes: this extend starts when the other lane's latest extend has finished, so the two alternate
+            if (lanes > 1 && run[l ^ 1].it > 0) RT_CUDA(cudaStreamWaitEvent(L.stream, run[l ^ 1].P->ev_extend, 0));
+            if (tick(L) < 0) return RT_ERR_CUDA;
+            if (P.suspend_below) {
+                if (count) k_extend_defer<true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
+                else k_extend_defer<false><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
+            } else if (exp_bits & 16u) {   // RT_EXP=16: streaming refill
+                if (count) k_extend_stream<true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
+                else k_extend_stream<false><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
+            } else if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
+            else if (exp_bits & 4u) k_extend<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);   // RT_EXP=4: fused loop
+            else k_extend<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
+            if (lanes > 1) RT_CUDA(cudaEventRecord(P.ev_extend, L.stream));
+            if (tick(L) < 0) return RT_ERR_CUDA;
+            if (P.suspend_below) k_shade_defer<<<P.grid_shade, 256, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
+            else if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
+            else k_shade<256><<<P.grid_shade, 256, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
+            if (tick(L) < 0) return RT_ERR_CUDA;
+            k_turnover<<<1, 1, 0, L.stream>>>(P.v, cur, L.fp.total_samples, L.d_live + (L.it % POLL_SLOTS));
+            RT_CUDA(cudaEventRecord(P.poll_ev[L.it % POLL_SLOTS], L.stream));
+            L.launches += 3;
+            L.iterations++;
+            if (L.it >= POLL_DEPTH) {
+                const uint64_t old = L.it - POLL_DEPTH;
                 RT_CUDA(cudaEventSynchronize(P.poll_ev[old % POLL_SLOTS]));
-                if (P.h_live[old % POLL_SLOTS] == 0) done = true;
+                if (P.h_live[old % POLL_SLOTS] == 0) L.done = true;
             }
-            if (it > max_iterations) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
+            if (L.it > L.max_iterations) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
+            L.it++;
         }
     }
-    if (tick() < 0) return RT_ERR_CUDA;
-    RT_CUDA(cudaEventRecord(P.ev_end, stream));
-    RT_CUDA(cudaMemcpyAsync(P.h_counters, P.v.c, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+    for (int l = 0; l < lanes; l++) {
+        LaneRun& L = run[l];
+        if (tick(L) < 0) return RT_ERR_CUDA;
+        RT_CUDA(cudaMemcpyAsync(L.P->h_counters, L.P->v.c, sizeof(Counters), cudaMemcpyDeviceToHost, L.stream));
+        if (l) {   // the caller's stream continues after the second lane
+            RT_CUDA(cudaEventRecord(L.P->ev_end, L.stream));
+            RT_CUDA(cudaStreamWaitEvent(stream, L.P->ev_end, 0));
+        }
+    }
+    RT_CUDA(cudaEventRecord(P0.ev_end, stream));
     RT_CUDA(cudaStreamSynchronize(stream));
     RT_CUDA(cudaGetLastError());
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
-        stats->samples = std::min<unsigned long long>(P.h_counters->next_sample, total);
-        stats->rays = P.h_counters->total_rays;
-        stats->iterations = iterations;
-        stats->kernel_launches = launches;
-        stats->nodes_visited = P.h_counters->nodes;
-        stats->prim_tests = P.h_counters->prim_tests;
-        stats->node_slots = P.h_counters->node_slots;
-        cudaEventElapsedTime(&stats->ms_total, P.ev_begin, P.ev_end);
-        if (timers) {   // per-kernel device time, summed over the iterations of this frame: 3 events per iteration + 1
-            double ext = 0, shd = 0, fin = 0;
-            for (size_t k = 0; k + 3 < n_timer; k += 3) {
-                float a = 0, b = 0, c = 0;
-                cudaEventElapsedTime(&a, P.timer_ev[k], P.timer_ev[k + 1]);
-                cudaEventElapsedTime(&b, P.timer_ev[k + 1], P.timer_ev[k + 2]);
-                cudaEventElapsedTime(&c, P.timer_ev[k + 2], P.timer_ev[k + 3]);
-                ext += a; shd += b; fin += c;
+        double ext = 0, shd = 0, fin = 0;
+        float ms_gen = 0.f;
+        for (int l = 0; l < lanes; l++) {
+            LaneRun& L = run[l];
+            const Counters& c = *L.P->h_counters;
+            stats->samples += std::min<unsigned long long>(c.next_sample, L.fp.total_samples);
+            stats->rays += c.total_rays;
+            stats->iterations += L.iterations;
+            stats->kernel_launches += L.launches;
+            stats->nodes_visited += c.nodes;
+            stats->prim_tests += c.prim_tests;
+            stats->node_slots += c.node_slots;
+            if (timers) {   // per-kernel device time, summed over the iterations of this frame: 3 events per iteration + 1
+                            // (two lanes: the intervals of the lanes overlap in time; the sums say what each kernel occupied)
+                const std::vector<cudaEvent_t>& ev = L.P->timer_ev;
+                for (size_t k = 0; k + 3 < L.n_timer; k += 3) {
+                    float a = 0, b = 0, d = 0;
+                    cudaEventElapsedTime(&a, ev[k], ev[k + 1]);
+                    cudaEventElapsedTime(&b, ev[k + 1], ev[k + 2]);
+                    cudaEventElapsedTime(&d, ev[k + 2], ev[k + 3]);
+                    ext += a; shd += b; fin += d;
+                }
+                if (l == 0 && L.n_timer) cudaEventElapsedTime(&ms_gen, P0.ev_begin, ev[0]);
             }
-            if (n_timer) cudaEventElapsedTime(&ms_gen, P.ev_begin, P.timer_ev[0]);
-            stats->ms_extend = (float)ext; stats->ms_shade = (float)shd; stats->ms_generate = ms_gen; stats->ms_finish = (float)fin;
         }
+        cudaEventElapsedTime(&stats->ms_total, P0.ev_begin, P0.ev_end);
+        stats->ms_extend = (float)ext; stats->ms_shade = (float)shd; stats->ms_generate = ms_gen; stats->ms_finish = (float)fin;
     }
     return RT_OK;
 }
