@@ -478,7 +478,8 @@ __device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView&
         if (tile >= n) break;
 
         // -- sort the tile by material class (counting sort: ballots -> [class][warp] table -> one warp scan)
-        {
+        uint32_t e = threadIdx.x | ((uint32_t)cls << 12);
+        if (!(fp.pad & 32u)) {   // RT_EXP=32: unsorted tiles (A/B of the sort: profiles/r01_v9_experiments.md)
             uint32_t rank = 0;
             #pragma unroll
             for (int k = 0; k < NC; k++) {
@@ -499,8 +500,8 @@ __device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView&
             __syncthreads();
             s_perm[s_cnt[cls * SHADE_WARPS + warp] + rank] = (uint16_t)(threadIdx.x | (cls << 12));
             __syncthreads();
+            e = s_perm[threadIdx.x];
         }
-        const uint32_t e = s_perm[threadIdx.x];
         const int k = (int)(e >> 12);
 
         // -- shade one path
