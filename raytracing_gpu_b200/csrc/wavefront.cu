@@ -78,6 +78,8 @@ struct RenderPool {
     cudaEvent_t poll_ev[POLL_SLOTS]{};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     int grid_extend = 0, grid_shade = 0, shade_block = 256;
+    cudaGraphExec_t graph_exec = nullptr;   // GRAPH_ITERS wavefront iterations as one CUDA graph (render_impl)
+    cudaStream_t capture_stream = nullptr;
     RenderPool* second = nullptr;        // two-lane rendering: the second lane's pools (owned)
     cudaStream_t own_stream = nullptr;   //   and its stream
     cudaEvent_t ev_extend = nullptr;     //   recorded after each extend launch of this lane
@@ -89,6 +91,8 @@ struct RenderPool {
 void render_pool_destroy(RenderPool* p) {
     if (!p) return;
     render_pool_destroy(p->second);
+    if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
+    if (p->capture_stream) cudaStreamDestroy(p->capture_stream);
     if (p->own_stream) cudaStreamDestroy(p->own_stream);
     if (p->ev_extend) cudaEventDestroy(p->ev_extend);
     for (int b = 0; b < 2; b++) { cudaFree(p->v.ray_o[b]); cudaFree(p->v.ray_d[b]); cudaFree(p->v.thr[b]); }
@@ -649,6 +653,7 @@ int pool_create(DeviceScene& ds, RenderPool** owner, uint32_t capacity, int lane
     for (auto& e : p->poll_ev) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     RT_CUDA(cudaEventCreate(&p->ev_begin)); RT_CUDA(cudaEventCreate(&p->ev_end));
     RT_CUDA(cudaEventCreateWithFlags(&p->ev_extend, cudaEventDisableTiming));
+    RT_CUDA(cudaStreamCreateWithFlags(&p->capture_stream, cudaStreamNonBlocking));
     int sms = 0;
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
     int occ = 0;
@@ -781,33 +786,72 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         k_generate<<<(n0 + 255) / 256, 256, 0, L.stream>>>(ds.view, L.P->v, L.fp, n0);
         L.launches += 1;
     }
-    for (bool all_done = false; !all_done;) {
+    // the three launches of one iteration (cur = parity of the iteration, slot = where turnover publishes the live count)
+    auto launch_iteration = [&](LaneRun& L, int cur, uint32_t slot, cudaStream_t s, bool timed) -> int {
+        RenderPool& P = *L.P;
+        if (timed && tick(L) < 0) return RT_ERR_CUDA;
+        if (P.suspend_below) {
+            if (count) k_extend_defer<true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
+            else k_extend_defer<false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
+        } else if (exp_bits & 16u) {   // RT_EXP=16: streaming refill
+            if (count) k_extend_stream<true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
+            else k_extend_stream<false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
+        } else if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
+        else if (exp_bits & 4u) k_extend<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);   // RT_EXP=4: fused loop
+        else k_extend<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
+        if (lanes > 1) RT_CUDA(cudaEventRecord(P.ev_extend, s));
+        if (timed && tick(L) < 0) return RT_ERR_CUDA;
+        if (P.suspend_below) k_shade_defer<<<P.grid_shade, 256, 0, s>>>(ds.view, P.v, L.fp, cur);
+        else if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, s>>>(ds.view, P.v, L.fp, cur);
+        else k_shade<256><<<P.grid_shade, 256, 0, s>>>(ds.view, P.v, L.fp, cur);
+        if (timed && tick(L) < 0) return RT_ERR_CUDA;
+        k_turnover<<<1, 1, 0, s>>>(P.v, cur, L.fp.total_samples, L.d_live + slot);
+        return RT_OK;
+    };
+    // One lane, no per-kernel timers: GRAPH_ITERS iterations go to the GPU as ONE CUDA graph.  Small frames and the drain of
+    // every frame are launch-bound (3 launches of a few microseconds per iteration); the graph takes the host out of that
+    // loop.  The graph is captured per call (the frame parameters are kernel arguments) and swapped into the pool's
+    // instantiated graph with cudaGraphExecUpdate — same topology, no re-instantiation.  The host stays one graph ahead of
+    // the live count it reads, so a finished frame costs at most one graph of empty iterations.
+    const bool use_graph = lanes == 1 && !timers && !run[0].done && !getenv("RT_NO_GRAPH");
+    if (use_graph) {
+        LaneRun& L = run[0];
+        RenderPool& P = *L.P;
+        constexpr int GRAPH_ITERS = POLL_SLOTS;     // a whole period of (parity, live-count slot)
+        cudaGraph_t g = nullptr;
+        RT_CUDA(cudaStreamBeginCapture(P.capture_stream, cudaStreamCaptureModeThreadLocal));
+        int rc = RT_OK;
+        for (int k = 0; k < GRAPH_ITERS && rc == RT_OK; k++) rc = launch_iteration(L, k & 1, (uint32_t)k, P.capture_stream, false);
+        const cudaError_t ce = cudaStreamEndCapture(P.capture_stream, &g);
+        if (rc < 0 || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); cudaGetLastError(); set_error("render: graph capture failed"); return RT_ERR_CUDA; }
+        if (P.graph_exec) {
+            cudaGraphExecUpdateResultInfo info;
+            if (cudaGraphExecUpdate(P.graph_exec, g, &info) != cudaSuccess) { cudaGetLastError(); cudaGraphExecDestroy(P.graph_exec); P.graph_exec = nullptr; }
+        }
+        if (!P.graph_exec && cuda_fail(cudaGraphInstantiate(&P.graph_exec, g, 0), "cudaGraphInstantiate", __FILE__, __LINE__)) { cudaGraphDestroy(g); return RT_ERR_CUDA; }
+        cudaGraphDestroy(g);
+        for (uint64_t gi = 0; !L.done; gi++) {
+            RT_CUDA(cudaGraphLaunch(P.graph_exec, stream));
+            RT_CUDA(cudaEventRecord(P.poll_ev[gi & 1], stream));
+            L.launches += 3 * GRAPH_ITERS; L.iterations += GRAPH_ITERS; L.it += GRAPH_ITERS;
+            if (gi >= 1) {   // the graph before this one: its last iteration's live count (a later one is as good: zero stays zero)
+                RT_CUDA(cudaEventSynchronize(P.poll_ev[(gi - 1) & 1]));
+                if (P.h_live[GRAPH_ITERS - 1] == 0) L.done = true;
+            }
+            if (L.it > L.max_iterations + 2 * GRAPH_ITERS) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
+        }
+    }
+    for (bool all_done = use_graph; !all_done;) {
         all_done = true;
         for (int l = 0; l < lanes; l++) {
             LaneRun& L = run[l];
             if (L.done) continue;
             all_done = false;
             RenderPool& P = *L.P;
-            const int cur = (int)(L.it & 1);
             // two lanes: this extend starts when the other lane's latest extend has finished, so the two alternate
             if (lanes > 1 && run[l ^ 1].it > 0) RT_CUDA(cudaStreamWaitEvent(L.stream, run[l ^ 1].P->ev_extend, 0));
-            if (tick(L) < 0) return RT_ERR_CUDA;
-            if (P.suspend_below) {
-                if (count) k_extend_defer<true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
-                else k_extend_defer<false><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
-            } else if (exp_bits & 16u) {   // RT_EXP=16: streaming refill
-                if (count) k_extend_stream<true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
-                else k_extend_stream<false><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
-            } else if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
-            else if (exp_bits & 4u) k_extend<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);   // RT_EXP=4: fused loop
-            else k_extend<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
-            if (lanes > 1) RT_CUDA(cudaEventRecord(P.ev_extend, L.stream));
-            if (tick(L) < 0) return RT_ERR_CUDA;
-            if (P.suspend_below) k_shade_defer<<<P.grid_shade, 256, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
-            else if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
-            else k_shade<256><<<P.grid_shade, 256, 0, L.stream>>>(ds.view, P.v, L.fp, cur);
-            if (tick(L) < 0) return RT_ERR_CUDA;
-            k_turnover<<<1, 1, 0, L.stream>>>(P.v, cur, L.fp.total_samples, L.d_live + (L.it % POLL_SLOTS));
+            const int rc = launch_iteration(L, (int)(L.it & 1), (uint32_t)(L.it % POLL_SLOTS), L.stream, true);
+            if (rc < 0) return rc;
             RT_CUDA(cudaEventRecord(P.poll_ev[L.it % POLL_SLOTS], L.stream));
             L.launches += 3;
             L.iterations++;
