@@ -454,12 +454,13 @@ __device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView&
     constexpr int NP = NQ;                           // "no path": the tile tail and (deferred extend) the holes suspended paths leave
     constexpr int NC = NP + 1;
     __shared__ uint32_t s_tile[2];                   // this tile / the next one (claimed while this one is shaded)
-    __shared__ uint32_t s_cnt[64];                   // [class][warp] counts -> exclusive offsets
+    constexpr int CELLS = NC * SHADE_WARPS <= 64 ? 2 : 4;   // class-table cells per lane of the scanning warp
+    __shared__ uint32_t s_cnt[32 * CELLS];           // [class][warp] counts -> exclusive offsets
     __shared__ uint16_t s_perm[SHADE_BLOCK];         // sorted rank -> tile-local index | class << 12
     __shared__ uint32_t s_wcont[SHADE_WARPS], s_wterm[SHADE_WARPS];
     __shared__ uint32_t s_base_b, s_base_f, s_nregen;
     __shared__ unsigned long long s_g0;
-    static_assert(NC * SHADE_WARPS <= 64, "class table must fit one warp scan of two cells per lane");
+    static_assert(NC * SHADE_WARPS <= 32 * CELLS, "class table must fit one warp scan");
 
     const int next = cur ^ 1;
     // tile index space: bounced paths, fresh camera paths, (deferred extend) the resumed paths that finished at positions >= capacity
@@ -469,7 +470,7 @@ __device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView&
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     auto pos_at = [&](uint32_t idx) { return DEFER && idx >= n_pool ? pv.capacity + (idx - n_pool) : pos_of(idx, n_b, n_pool, pv.capacity); };
-    if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x < 32 * CELLS) s_cnt[threadIdx.x] = 0;
     if (threadIdx.x == 0) s_tile[0] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
     __syncthreads();
     auto class_of = [&](uint32_t tile) {             // material class of this thread's path in `tile` (NQ past the end)
@@ -493,13 +494,15 @@ __device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView&
             }
             __syncthreads();
             if (warp == 0) {
-                const uint32_t v0 = s_cnt[2 * lane], v1 = s_cnt[2 * lane + 1];
-                uint32_t x = v0 + v1;
+                uint32_t v[CELLS], sum = 0;
+                #pragma unroll
+                for (int c = 0; c < CELLS; c++) { v[c] = s_cnt[CELLS * lane + c]; sum += v[c]; }
+                uint32_t x = sum;
                 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)lane >= o) x += y; }
-                const uint32_t ex = x - (v0 + v1);
-                s_cnt[2 * lane] = ex;
-                s_cnt[2 * lane + 1] = ex + v0;
+                uint32_t ex = x - sum;
+                #pragma unroll
+                for (int c = 0; c < CELLS; c++) { s_cnt[CELLS * lane + c] = ex; ex += v[c]; }
             }
             __syncthreads();
             s_perm[s_cnt[cls * SHADE_WARPS + warp] + rank] = (uint16_t)(threadIdx.x | (cls << 12));
@@ -659,8 +662,9 @@ int pool_create(DeviceScene& ds, RenderPool** owner, uint32_t capacity, int lane
     int occ = 0;
     RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend<false, true>, EXTEND_BLOCK, 0));
     p->grid_extend = sms * std::max(occ, 1);
-    p->shade_block = (getenv("RT_EXP") && (atoi(getenv("RT_EXP")) & 8)) ? 128 : 256;
+    p->shade_block = (getenv("RT_EXP") && (atoi(getenv("RT_EXP")) & 8)) ? 128 : (getenv("RT_EXP") && (atoi(getenv("RT_EXP")) & 64)) ? 512 : 256;
     if (p->shade_block == 128) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<128>, 128, 0));
+    else if (p->shade_block == 512) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<512>, 512, 0));
     else RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<256>, 256, 0));
     p->grid_shade = sms * std::max(occ, 1);
     if (p->suspend_below) {
@@ -803,6 +807,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         if (timed && tick(L) < 0) return RT_ERR_CUDA;
         if (P.suspend_below) k_shade_defer<<<P.grid_shade, 256, 0, s>>>(ds.view, P.v, L.fp, cur);
         else if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, s>>>(ds.view, P.v, L.fp, cur);
+        else if (P.shade_block == 512) k_shade<512><<<P.grid_shade, 512, 0, s>>>(ds.view, P.v, L.fp, cur);   // RT_EXP=64
         else k_shade<256><<<P.grid_shade, 256, 0, s>>>(ds.view, P.v, L.fp, cur);
         if (timed && tick(L) < 0) return RT_ERR_CUDA;
         k_turnover<<<1, 1, 0, s>>>(P.v, cur, L.fp.total_samples, L.d_live + slot);
