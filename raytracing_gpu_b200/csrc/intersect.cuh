@@ -233,24 +233,19 @@ __device__ __forceinline__ void prim_attr(const SceneView& sv, const DPrim& p, c
 }
 
 // ---- constant_medium::hit — constant_medium.h:34-70 -------------------------------------------------
-// closest hit over a medium's boundary primitives, list semantics (hittable_list.h:23-39: later wins ties).
-// The boundary primitives of one medium nearly always share ONE wrapper chain (a box under translate(rotate_y)),
-// so the object-space ray is cached per chain across the primitives and across both boundary queries.
+// The two boundary queries of constant_medium::hit (constant_medium.h:36-40): the closest hit of the boundary list in
+// (-inf, inf), then the closest one from just behind it, (t1 + 0.0001, inf) — list semantics, hittable_list.h:23-39:
+// a candidate is accepted unless t < t_min or t > closest-so-far, later objects win ties.
+// Whether a primitive offers a candidate at all, and at which t, does not depend on the query range (a rect's bounds test,
+// a triangle's barycentric tests, a sphere's near root), so each boundary primitive is intersected ONCE with the range
+// wide open; both queries then replay the list's accept / shrink sequence over the stored candidates, comparison for
+// comparison (NaN and infinite t included).  Half the primitive tests of a medium: Cornell smoke extend -13 %, step +9.3 % (the two
+// box-bounded media there cost more than the BVH).  Falls back to intersecting per query where the candidate itself
+// depends on the range (RT_SEM_SPHERE_FAR_ROOT) or the boundary has more than RT_BOUNDARY_CACHE primitives.
+// The boundary primitives of one medium nearly always share ONE wrapper chain (a box under translate(rotate_y)), so the
+// object-space ray is cached per chain across the primitives.
+#define RT_BOUNDARY_CACHE 8
 struct ChainCache { uint32_t chain; Ray ray; };
-
-__device__ __forceinline__ bool boundary_t(const SceneView& sv, const DMedium& m, const Ray& r, ChainCache& cc, float t_min, float t_max, float& t) {
-    bool any = false;
-    float closest = t_max;
-    for (uint32_t i = 0; i < m.bprim_count; i++) {
-        const DPrim p = sv.bprims[m.bprim_first + i];
-        const uint32_t chain = prim_chain(p);
-        if (chain != cc.chain) { cc.ray = to_object_space(sv, chain, r); cc.chain = chain; }
-        float tt;
-        if (prim_t_local(p, cc.ray, t_min, closest, sv.semantics, tt)) { any = true; closest = tt; }
-    }
-    t = closest;
-    return any;
-}
 
 // Returns true and the hit distance when the medium scatters the ray before t_max.  `xi()` yields the uniform
 // draw; it is only evaluated when the ray really crosses the boundary (constant_medium.h:57).
@@ -258,16 +253,36 @@ template <class XiFn>
 __device__ __forceinline__ bool medium_t(const SceneView& sv, const DMedium& m, const Ray& world, float t_min, float t_max, XiFn&& xi, float& t) {
     const Ray r = to_object_space(sv, m.chain, world);
     ChainCache cc; cc.chain = 0; cc.ray = r;
-    // entry, then exit from just behind the entry (constant_medium.h:33-37).  ONE instance of the boundary code, looped:
-    // k_extend's code size decides its instruction-cache hit rate on scenes with media (profiles/r01_v6_*.md)
+    const bool per_query = (sv.semantics & RT_SEM_SPHERE_FAR_ROOT) != 0 || m.bprim_count > RT_BOUNDARY_CACHE;
+    float cand[RT_BOUNDARY_CACHE];
+    uint32_t offered = 0;
+    // ONE instance of the boundary code, looped: k_extend's code size decides its instruction-cache hit rate on scenes
+    // with media (profiles/r01_v6_*.md)
     float tq[2] = {0.f, 0.f};
     float lo = -INFINITY;
     #pragma unroll 1
     for (int q = 0; q < 2; q++) {
-        float tt;
-        if (!boundary_t(sv, m, r, cc, lo, INFINITY, tt)) return false;
-        tq[q] = tt;
-        lo = tt + 0.0001f;
+        bool any = false;
+        float closest = INFINITY;
+        for (uint32_t i = 0; i < m.bprim_count; i++) {
+            float tt = 0.f;
+            bool ok;
+            if (q == 0 || per_query) {
+                const DPrim p = sv.bprims[m.bprim_first + i];
+                const uint32_t chain = prim_chain(p);
+                if (chain != cc.chain) { cc.ray = to_object_space(sv, chain, r); cc.chain = chain; }
+                ok = prim_t_local(p, cc.ray, per_query ? lo : -INFINITY, per_query ? closest : INFINITY, sv.semantics, tt);
+                if (!per_query) { cand[i] = tt; offered |= (ok ? 1u : 0u) << i; }
+            } else {
+                tt = cand[i];
+                ok = (offered >> i) & 1u;
+            }
+            if (!per_query) ok = ok && !(tt < lo) && !(tt > closest);       // the range test the primitive would have made
+            if (ok) { any = true; closest = tt; }
+        }
+        if (!any) return false;
+        tq[q] = closest;
+        lo = closest + 0.0001f;
     }
     float t1 = tq[0], t2 = tq[1];
     if (t1 < t_min) t1 = t_min;
