@@ -344,12 +344,15 @@ __device__ __forceinline__ void closest_medium(const SceneView& sv, const Ray& r
     for (uint32_t a = 0; a < sv.n_active_media; a++) {
         const uint32_t m = sv.active_media[a];
         const DMedium med = sv.media[m];
-        {   // the ray's LINE against the medium's world box: a miss means no boundary crossing at any t
+        {   // the ray's LINE against the medium's (padded) world box: a miss means no boundary crossing at any t.  And the
+            // SEGMENT [t_min, closest surface]: constant_medium::hit clips entry and exit to it and gives up when nothing is
+            // left (constant_medium.h:42-46), which is certain when the box is entered behind the closest surface or left
+            // before t_min — no need to intersect the boundary to find that out
             const float x0 = fmaf(med.lo.x, ix, -ox), x1 = fmaf(med.hi.x, ix, -ox), y0 = fmaf(med.lo.y, iy, -oy), y1 = fmaf(med.hi.y, iy, -oy);
             const float z0 = fmaf(med.lo.z, iz, -oz), z1 = fmaf(med.hi.z, iz, -oz);
             const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
             const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
-            if (!(tn <= tf)) continue;
+            if (!(tn <= tf) || tn > best.t || tf < t_min) continue;
         }
         float t;
         if (medium_t(sv, med, ray, t_min, best.t, [&]() { return xi_of(m); }, t)) { best.t = t; best.prim = -2 - (int)m; }
