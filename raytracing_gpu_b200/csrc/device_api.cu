@@ -4,6 +4,9 @@
 #include "traverse.cuh"
 
 #include <cstdio>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -66,6 +69,15 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     cudaEvent_t e0, e1;
     RT_CUDA(cudaEventCreate(&e0)); RT_CUDA(cudaEventCreate(&e1));
     RT_CUDA(cudaEventRecord(e0, st));
+    // RT_COMMIT_TRACE=1: host wall clock of the commit phases on stderr (tools/commit_probe.py)
+    const bool trace = getenv("RT_COMMIT_TRACE") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!trace) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[commit] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
 
     std::vector<DPrim> prims(fs.prims.size()), bprims(fs.bprims.size());
     std::vector<uint32_t> leaf_ids(fs.prims.size());
@@ -88,6 +100,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
         const bool inert = m.bprim_count == 1 && (fs.bprims[m.bprim_first].type == RT_PRIM_SPHERE || fs.bprims[m.bprim_first].type == RT_PRIM_MOVING_SPHERE);
         if (!inert || (hs.semantics & RT_SEM_SPHERE_FAR_ROOT)) active_media.push_back((uint32_t)i);   // with the far root they do scatter
     }
+    lap("prims -> device records");
     std::vector<DPerlin> perlins(fs.perlins.size());
     for (size_t i = 0; i < fs.perlins.size(); i++) {
         for (int k = 0; k < 256; k++) perlins[i].ranvec[k] = make_float4(fs.perlins[i].ranvec[3 * k], fs.perlins[i].ranvec[3 * k + 1], fs.perlins[i].ranvec[3 * k + 2], 0.f);
@@ -118,6 +131,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
         images[i] = DImage{ds.image_objs[i], im.width, im.height};
     }
 
+    lap("perlin + image textures");
     void *d_prims_in = nullptr, *d_leaf_in = nullptr;
     int rc;
     if ((rc = upload(&d_prims_in, prims, st)) < 0) return rc;
@@ -133,6 +147,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     if ((rc = upload(&ds.d_perlins, perlins, st)) < 0) return rc;
     if ((rc = upload(&ds.d_images, images, st)) < 0) return rc;
 
+    lap("cudaMalloc + H2D (queued)");
     SceneView& v = ds.view;
     v.bprims = (const DPrim*)ds.d_bprims; v.media = (const DMedium*)ds.d_media;
     v.tri_attrs = (const rt_flat_tri_attr*)ds.d_tri_attrs; v.xops = (const rt_flat_xop*)ds.d_xops;
@@ -154,10 +169,12 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     RT_CUDA(cudaEventRecord(b0, st));
     rc = build_lbvh(ds, (const DPrim*)d_prims_in, (const uint32_t*)d_leaf_in, v.n_prims, t_lo, t_hi, st);
     if (rc < 0) return rc;
+    lap("build_lbvh");
     if ((rc = compute_medium_bounds(ds, t_lo, t_hi, st)) < 0) return rc;
     RT_CUDA(cudaEventRecord(b1, st));
     RT_CUDA(cudaStreamSynchronize(st));
     cudaFree(d_prims_in); cudaFree(d_leaf_in);
+    lap("medium bounds + sync + free");
     cudaEventElapsedTime(&ds.build.ms_upload, e0, e1);
     cudaEventElapsedTime(&ds.build.ms_total, e0, b1);
     ds.build.n_prims = v.n_prims;
