@@ -79,10 +79,18 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
         t_last = now;
     };
 
-    std::vector<DPrim> prims(fs.prims.size()), bprims(fs.bprims.size());
-    std::vector<uint32_t> leaf_ids(fs.prims.size());
-    for (size_t i = 0; i < fs.prims.size(); i++) { prims[i] = to_dprim(fs.prims[i]); leaf_ids[i] = fs.prims[i].leaf_id; }
-    for (size_t i = 0; i < fs.bprims.size(); i++) bprims[i] = to_dprim(fs.bprims[i]);
+    if (fs.commit_leaf_ids.size() != fs.prims.size() || fs.commit_bprims.size() != fs.bprims.size() * sizeof(DPrim)) {   // first commit of this flattening
+        fs.commit_prims.resize(fs.prims.size() * sizeof(DPrim));
+        fs.commit_bprims.resize(fs.bprims.size() * sizeof(DPrim));
+        fs.commit_leaf_ids.resize(fs.prims.size());
+        DPrim* dp = reinterpret_cast<DPrim*>(fs.commit_prims.data());
+        DPrim* db = reinterpret_cast<DPrim*>(fs.commit_bprims.data());
+        for (size_t i = 0; i < fs.prims.size(); i++) { dp[i] = to_dprim(fs.prims[i]); fs.commit_leaf_ids[i] = fs.prims[i].leaf_id; }
+        for (size_t i = 0; i < fs.bprims.size(); i++) db[i] = to_dprim(fs.bprims[i]);
+    }
+    const std::vector<uint8_t>&prims = fs.commit_prims, &bprims = fs.commit_bprims;
+    const std::vector<uint32_t>& leaf_ids = fs.commit_leaf_ids;
+    const size_t n_prims = fs.prims.size();
     std::vector<DMedium> media(fs.media.size());
     for (size_t i = 0; i < fs.media.size(); i++) {
         const rt_flat_medium& m = fs.media[i];
@@ -114,11 +122,15 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     std::vector<DImage> images(fs.images.size());
     for (size_t i = 0; i < fs.images.size(); i++) {
         const rt_flat_image& im = fs.images[i];
-        std::vector<uint8_t> rgba((size_t)im.width * im.height * 4);
-        const uint8_t* src = fs.image_bytes.data() + im.offset;
-        for (size_t k = 0; k < (size_t)im.width * im.height; k++) {
-            rgba[4 * k] = src[k * im.bytes_per_pixel]; rgba[4 * k + 1] = src[k * im.bytes_per_pixel + 1];
-            rgba[4 * k + 2] = src[k * im.bytes_per_pixel + 2]; rgba[4 * k + 3] = 255;
+        if (fs.commit_rgba.size() != fs.images.size()) fs.commit_rgba.assign(fs.images.size(), std::vector<uint8_t>());
+        std::vector<uint8_t>& rgba = fs.commit_rgba[i];
+        if (rgba.size() != (size_t)im.width * im.height * 4) {   // first commit of this flattening
+            rgba.resize((size_t)im.width * im.height * 4);
+            const uint8_t* src = fs.image_bytes.data() + im.offset;
+            for (size_t k = 0; k < (size_t)im.width * im.height; k++) {
+                rgba[4 * k] = src[k * im.bytes_per_pixel]; rgba[4 * k + 1] = src[k * im.bytes_per_pixel + 1];
+                rgba[4 * k + 2] = src[k * im.bytes_per_pixel + 2]; rgba[4 * k + 3] = 255;
+            }
         }
         cudaChannelFormatDesc desc = cudaCreateChannelDesc<uchar4>();
         RT_CUDA(cudaMallocArray(&ds.image_arrays[i], &desc, im.width, im.height));
@@ -154,7 +166,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device) {
     v.chains = (const rt_flat_chain*)ds.d_chains; v.materials = (const rt_flat_material*)ds.d_materials;
     v.textures = (const rt_flat_texture*)ds.d_textures; v.perlins = (const DPerlin*)ds.d_perlins;
     v.images = (const DImage*)ds.d_images;
-    v.n_prims = (uint32_t)prims.size(); v.n_media = (uint32_t)media.size();
+    v.n_prims = (uint32_t)n_prims; v.n_media = (uint32_t)media.size();
     v.active_media = (const uint32_t*)ds.d_active_media; v.n_active_media = (uint32_t)active_media.size();
     v.camera = fs.hdr.camera;
     std::memcpy(v.background, fs.hdr.background, sizeof(v.background));
