@@ -41,6 +41,7 @@ WORKLOADS = {
     "final": ("final", 1920, 16.0 / 9.0, 1024, "Next-Week final scene 1920x1079 1024spp/GPU depth50 (BASELINE config 3)"),
     "cornell_smoke": ("cornell_smoke", 800, 1.0, 1024, "Cornell box with smoke 800x800 1024spp/GPU depth50 (BASELINE config 2)"),
     "big1": ("big1", 400, 16.0 / 9.0, 16, "RTIOW random spheres 400x224 16spp depth50 (BASELINE config 1)"),
+    "two_perlin": ("two_perlin", 1280, 16.0 / 9.0, 256, "two Perlin-noise spheres 1280x719 256spp/GPU depth50 (scenes.h:248; texture-bound shade)"),
     "mesh": ("mesh", 1920, 16.0 / 9.0, 256, "procedural 1M-triangle mesh + ground 1920x1079 256spp/GPU (BASELINE config 4 stand-in)"),
 }
 
