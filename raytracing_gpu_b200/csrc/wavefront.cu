@@ -251,7 +251,10 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
 // iteration raised the lane utilisation of the node loop just as much but paid for it with the latency of the longest
 // walks at the end of every iteration (profiles/r01_v9_experiments.md).
 template <bool COUNT>
-__global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend_defer(SceneView sv, PoolView pv, FrameParams fp, int cur, uint32_t suspend_below) {
+#ifndef DEFER_MIN_BLOCKS
+#define DEFER_MIN_BLOCKS EXTEND_MIN_BLOCKS
+#endif
+__global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer(SceneView sv, PoolView pv, FrameParams fp, int cur, uint32_t suspend_below) {
     const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
     const int rd = cur ^ 1, wr = cur;
     const uint32_t n_c = pv.c->cont[rd].n, n_c32 = (n_c + 31u) & ~31u;   // work index space: continuation records (padded to whole warps), then the pool
