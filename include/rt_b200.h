@@ -119,22 +119,52 @@ int rt_scene_hash(rt_scene* s, uint64_t* out);
 int rt_image_height(int width, float aspect);
 
 /* ---- device side ---- */
-enum rt_builder { RT_BUILDER_KARRAS = 0, RT_BUILDER_PLOC = 1, RT_BUILDER_HOST_SAH = 2 };
+enum rt_builder { RT_BUILDER_KARRAS = 0, RT_BUILDER_PLOC = 1, RT_BUILDER_HOST_SAH = 2, RT_BUILDER_GPU_SAH = 3 };
 
 typedef struct rt_build_stats {
     uint32_t n_prims, n_nodes;
     float ms_upload, ms_morton, ms_sort, ms_hierarchy, ms_refit, ms_collapse, ms_total;
-    uint32_t bvh_depth;      /* PLOC builds: depth of the tree */
-    uint32_t build_rounds;   /* PLOC builds: clustering rounds */
-    float sah_internal;      /* PLOC builds: sum of internal-node surface areas / root area */
+    uint32_t bvh_depth;      /* depth of the binary tree */
+    uint32_t build_rounds;   /* PLOC builds: clustering rounds; SAH sweep on the GPU: levels */
+    float sah_internal;      /* sum of internal-node surface areas / root area */
     uint32_t ploc_radius;    /* PLOC builds: neighbour search radius of the tree that was kept */
     uint32_t builder;        /* rt_builder: which hierarchy builder produced the tree */
-    uint32_t reserved[3];
+    uint32_t n_wide_nodes;   /* > 0: the traversal walks the compressed 4-wide layout (this many 64-byte nodes) */
+    float ms_host;           /* host wall clock of the whole rt_scene_commit call */
+    uint32_t reserved[1];
 } rt_build_stats;
+
+/* How rt_scene_commit_ex builds the acceleration structure.  Zero-initialise for the defaults.  (Round 1 read these
+ * from environment variables; a library behind a C-ABI takes them as arguments.) */
+enum rt_build_choice {
+    RT_BUILD_AUTO = 0,       /* SAH sweep on the GPU up to sah_max_prims primitives, PLOC (GPU) with a SAH-swept top above */
+    RT_BUILD_KARRAS = 1,     /* Morton-prefix hierarchy (Karras 2012) + bottom-up refit: A/B only */
+    RT_BUILD_PLOC = 2,       /* parallel locally-ordered clustering on the GPU */
+    RT_BUILD_HOST_SAH = 3,   /* round 1's host-thread sweep: kept as the checker of the GPU sweep (same tree, bit for bit) */
+    RT_BUILD_GPU_SAH = 4     /* full-sweep SAH, top-down, on the GPU */
+};
+enum rt_wide_choice { RT_WIDE_AUTO = 0, RT_WIDE_OFF = 1, RT_WIDE_ON = 2 };
+enum rt_build_flags { RT_BUILD_TRACE = 1 /* host wall clock of the commit phases on stderr */ };
+typedef struct rt_build_settings {
+    uint32_t builder;        /* rt_build_choice */
+    uint32_t sah_max_prims;  /* RT_BUILD_AUTO: largest scene the SAH sweep takes; 0 = 65536 */
+    uint32_t ploc_radius;    /* PLOC neighbour search radius; 0 = chosen per scene */
+    uint32_t ploc_top;       /* PLOC hands the top of the tree to the SAH sweep once this many clusters are left; 0 = 32768 */
+    uint32_t wide_nodes;     /* rt_wide_choice: collapse the binary tree into 4-wide nodes with 8-bit child boxes */
+    uint32_t flags;          /* rt_build_flags */
+    uint32_t reserved[10];
+} rt_build_settings;
 
 /* Flatten (if needed), upload to `device` and build the LBVH there.  Replaces the one-thread device
  * constructors create_*_world<<<1,1>>> + bvh_node::bvh_node (scenes.h:82..., bvh.h:270-346). */
 int rt_scene_commit(rt_scene* s, int device, rt_build_stats* stats_or_null);
+int rt_scene_commit_ex(rt_scene* s, int device, const rt_build_settings* settings_or_null, rt_build_stats* stats_or_null);
+
+/* Copies the binary BVH of the committed scene to the host: rt_build_stats::n_nodes records of 64 bytes (16 words:
+ * child 0 lo.x hi.x lo.y hi.y | child 1 lo.x hi.x lo.y hi.y | child 0 lo.z hi.z, child 1 lo.z hi.z | child codes, 2 pad words;
+ * a child code >= 0 is a node index, < 0 the complement of a primitive's position in leaf order).  For tools and tests
+ * (tree equality of two builders).  Returns the number of nodes. */
+int rt_scene_bvh_nodes(rt_scene* s, void* buf, size_t cap_bytes);
 
 /* Closest hit for a caller-supplied ray set — what color_f asks of the world at render.h:63.
  * rays: n x 7 floats (origin, direction, time), host memory.  xi: NULL, or n floats in (0,1]: the value used
@@ -169,8 +199,22 @@ typedef struct rt_render_settings {  /* replaces render_settings (render.h:21-50
                                         b with b % tile_count == tile_index (blocks of RT_TILE_BLOCK_PIXELS consecutive
                                         pixels in film order = 32 tiles of 8x4); the other pixels of the buffer are left
                                         untouched, so per-rank buffers still sum with ONE reduce.  0 / 1 = whole frame */
-    uint32_t reserved[5];
+    uint32_t extend_defer;           /* rt_defer_choice: deferred extend (stragglers of a warp are suspended and resumed 32 to
+                                        a warp in the next iteration).  0 = automatic (on above 65 536 primitives), 1 = off,
+                                        n >= 2 = on, a warp suspends once <= n - 1 of its rays are still walking */
+    uint32_t traversal;              /* 0 = the default k_extend variant; RT_TRAVERSAL_FORCE | bits selects one for A/B:
+                                        1 = stack entries carry their entry distance and are culled at pop, 2 = short stack in
+                                        shared memory (trees up to 16 levels), 4 = min/max plane selection on the ALU pipe */
+    uint32_t debug_flags;            /* rt_debug_flags */
+    uint32_t reserved[2];
 } rt_render_settings;
+enum rt_defer_choice { RT_DEFER_AUTO = 0, RT_DEFER_OFF = 1 };
+enum rt_traversal_bits { RT_TRAVERSAL_FORCE = 0x100, RT_TRAVERSAL_DEFAULT_BITS = 0 };
+enum rt_debug_flags {
+    RT_DEBUG_NO_GRAPH = 1,     /* direct kernel launches instead of the CUDA graph of 8 iterations */
+    RT_DEBUG_RASTER_FILM = 2,  /* samples walk the film row by row instead of in 8x4 tiles */
+    RT_DEBUG_BLOCK_SHADE = 4   /* round 1's block-tile shade kernel (same-box A/B of the warp-tile kernel) */
+};
 
 typedef struct rt_render_stats {
     uint64_t samples;       /* camera paths started */
@@ -196,6 +240,9 @@ int rt_render(rt_scene* s, const rt_render_settings* settings, float* out_rgb, r
  * reduce) and divides by samples_per_pixel. */
 int rt_render_device(rt_scene* s, const rt_render_settings* settings, float* d_accum_rgb, void* cuda_stream,
                      rt_render_stats* stats_or_null);
+
+/* FP32 peak of `device` measured with an FMA microbenchmark (the denominator of bench.py's roofline_fp32). */
+int rt_measure_fp32_peak(int device, double* tflops);
 
 /* Reference-exact 8-bit output stage (color.h:19-49): gamma-2, clamp to 0.999, *256, row flip. Host only.
  * in: linear means, row 0 = bottom; out: width*height*3 bytes, row 0 = top. */

@@ -7,11 +7,12 @@
 //   radix sort    LSD, 8 bits per pass, (u64 key, u32 value), 3 kernels per pass: per-tile histogram,
 //                 single-block exclusive scan of the digit-major table, stable scatter (warp match ranking);
 //                 passes whose digit is constant over all keys are skipped
-// then ONE of three hierarchies over the sorted leaves (rt_build_stats::builder; RT_BVH=sah|ploc|karras forces one):
-//   host SAH      scenes up to RT_SAH_MAX (65536) primitives: full-sweep SAH, top-down, O(n log n), up to 16 host
-//                 threads — 1.4 ms for the 3407 primitives of the Next-Week final scene, 16 ms for 64 k; 11-16 % fewer
-//                 node visits per ray than PLOC on every scene measured (profiles/r01_v8_sah.md)
-//   PLOC          everything larger, on the device: locally-ordered clustering, 1 M triangles in 4 ms
+// then ONE hierarchy over the sorted leaves (rt_build_settings::builder chooses, rt_build_stats::builder reports):
+//   SAH sweep     scenes up to 65 536 primitives: full-sweep SAH, top-down, on the GPU (level-synchronous, block scans);
+//                 11-16 % fewer node visits per ray than PLOC on every scene measured (profiles/r01_v8_sah.md).  Round 1
+//                 ran this sweep on host threads; that builder is kept as the checker (same tree, bit for bit)
+//   PLOC          everything larger, on the device: locally-ordered clustering, 1 M triangles in 4 ms; the top of the
+//                 tree (the last 32 k clusters) goes to the SAH sweep
 //   Karras        Morton-prefix hierarchy + atomic bottom-up refit (A/B only)
 // and the primitives are permuted into leaf order.  Nodes are 64 bytes (the parent holds both child boxes), root = 0.
 #include "device_scene.cuh"
@@ -220,8 +221,10 @@ constexpr int SORT_THREADS = 256;
 constexpr int SORT_ROUNDS = 8;                         // keys per thread
 constexpr int SORT_TILE = SORT_THREADS * SORT_ROUNDS;  // keys per block
 
+// blockIdx.y = batch: independent sorts of the same length laid out back to back (the three axis orders of the SAH sweep)
 __global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const uint64_t* keys, uint32_t n, int shift, uint32_t* counts /* [256][nblocks] */) {
     __shared__ uint32_t hist[256];
+    keys += (size_t)blockIdx.y * n; counts += (size_t)blockIdx.y * 256 * gridDim.x;
     hist[threadIdx.x] = 0;
     __syncthreads();
     const uint32_t base = blockIdx.x * SORT_TILE;
@@ -238,6 +241,7 @@ __global__ void __launch_bounds__(1024) k_sort_scan(uint32_t* counts, uint32_t l
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry;
     __shared__ uint32_t trivial;
+    counts += (size_t)blockIdx.y * len; pass_is_trivial += blockIdx.y;
     if (threadIdx.x == 0) { carry = 0; trivial = 0; }
     __syncthreads();
     // trivial-pass detection: digit d is constant iff sum_b counts[d][b] == n
@@ -276,6 +280,8 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const uint64_t* k
     __shared__ uint32_t warp_count[SORT_THREADS / 32][256];    // per round
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t base = blockIdx.x * SORT_TILE;
+    keys_in += (size_t)blockIdx.y * n; vals_in += (size_t)blockIdx.y * n; keys_out += (size_t)blockIdx.y * n; vals_out += (size_t)blockIdx.y * n;
+    offsets += (size_t)blockIdx.y * 256 * gridDim.x; pass_is_trivial += blockIdx.y;
     if (*pass_is_trivial) {   // constant digit: order is unchanged, plain copy keeps the ping-pong consistent
         for (int r = 0; r < SORT_ROUNDS; r++) {
             const uint32_t i = base + r * SORT_THREADS + threadIdx.x;
@@ -556,26 +562,309 @@ __global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_merge(const int* nn, int n,
     cid_out[p] = id; lo_out[p] = alo; hi_out[p] = ahi;
 }
 
-template <class T> cudaError_t dalloc(T** p, size_t count) { return cudaMalloc((void**)p, (count ? count : 1) * sizeof(T)); }
+// ---------------------------------------------------------------------------------------------------
+// Full-sweep SAH hierarchy on the GPU (the default for scenes up to 65 536 primitives, and the top of PLOC trees)
+//
+// Top-down, one primitive per leaf: at every node every split position along every axis (primitives ordered by box
+// centre) is scored with area(L) * |L| + area(R) * |R| and the best of the 3 x (n - 1) candidates wins — the sweep
+// round 1 ran on host threads (SahBuilder below, kept as its checker), restated for the device:
+//   * the three orders are sorted ONCE (radix sort of the centre keys, the three axes batched in one launch);
+//     a split stably partitions the other two, so every subtree owns the same range of all three arrays;
+//   * the tree is built level by level: the segments (= tree nodes) of one level sit in a queue, blocks of 256 threads
+//     claim them one at a time; a segment's prefix / suffix box areas are chunked block scans (box union is exact and
+//     associative, so the scan yields the very floats the sequential sweep computes), the best split a block-wide
+//     lexicographic (cost, axis, position) minimum — the first strict minimum the host loop would keep;
+//   * a subtree over k primitives owns k - 1 consecutive nodes in preorder (left child = me + 1, right child =
+//     me + |L|), so node indices need no allocation, and both child boxes are known at split time: the parent writes
+//     its finished 64-byte node immediately — no bottom-up pass;
+//   * no host round trips: the level loop is a fixed number of launches (a level with an empty queue exits at once),
+//     the host reads one control block at the end.
+// The result equals the host sweep's tree bit for bit (tests/test_gpu.py::test_gpu_sah_sweep_equals_host_sweep).
+// ---------------------------------------------------------------------------------------------------
+constexpr int SAH_THREADS = 256, SAH_ITEMS = 4, SAH_CHUNK = SAH_THREADS * SAH_ITEMS, SAH_WARPS = SAH_THREADS / 32;
+constexpr int SAH_MAX_LEVELS = RT_STACK_DEPTH;
+
+struct B6 { float lx, ly, lz, hx, hy, hz; };
+__device__ __forceinline__ B6 b6_empty() { return B6{INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY}; }
+__device__ __forceinline__ B6 b6_unite(const B6& a, const B6& b) {
+    return B6{fminf(a.lx, b.lx), fminf(a.ly, b.ly), fminf(a.lz, b.lz), fmaxf(a.hx, b.hx), fmaxf(a.hy, b.hy), fmaxf(a.hz, b.hz)};
+}
+__device__ __forceinline__ float b6_half_area(const B6& b) { const float x = b.hx - b.lx, y = b.hy - b.ly, z = b.hz - b.lz; return x * y + y * z + z * x; }
+__device__ __forceinline__ B6 b6_shfl_up(const B6& b, int o) {
+    return B6{__shfl_up_sync(0xffffffffu, b.lx, o), __shfl_up_sync(0xffffffffu, b.ly, o), __shfl_up_sync(0xffffffffu, b.lz, o),
+              __shfl_up_sync(0xffffffffu, b.hx, o), __shfl_up_sync(0xffffffffu, b.hy, o), __shfl_up_sync(0xffffffffu, b.hz, o)};
+}
+__device__ __forceinline__ B6 b6_shfl_xor(const B6& b, int o) {
+    return B6{__shfl_xor_sync(0xffffffffu, b.lx, o), __shfl_xor_sync(0xffffffffu, b.ly, o), __shfl_xor_sync(0xffffffffu, b.lz, o),
+              __shfl_xor_sync(0xffffffffu, b.hx, o), __shfl_xor_sync(0xffffffffu, b.hy, o), __shfl_xor_sync(0xffffffffu, b.hz, o)};
+}
+
+struct SahSeg { uint32_t first, count; int me; uint32_t level; };
+struct SahCtl {
+    uint32_t nseg[SAH_MAX_LEVELS + 2];     // segments queued for level l
+    uint32_t cursor[SAH_MAX_LEVELS + 2];   // ... and the next one to claim
+    uint32_t depth, too_deep;
+    double area_sum;
+    float root_lo[3], root_hi[3];
+};
+struct SahArgs {
+    const float4* lo; const float4* hi;    // leaf boxes; lo.w = depth of the subtree below the leaf when has_depth
+    const int* leaf_code;                  // child code of leaf i (nullptr: ~i, primitive i)
+    int has_depth;
+    uint32_t* order[3];                    // the leaves in the three axis orders
+    uint32_t* scratch;                     // [n] by position
+    uint8_t* goes_right;                   // [n] by leaf
+    float* right_area;                     // [n] by position
+    SahSeg* queue[2];
+    SahCtl* ctl;
+    BNode* nodes;
+    uint32_t n;
+};
+
+__global__ void k_sah_keys(const float4* lo, const float4* hi, uint32_t n, uint64_t* keys /* [3][n] */, uint32_t* vals /* [3][n] */) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 l = lo[i], h = hi[i];
+    const float c[3] = {l.x + h.x, l.y + h.y, l.z + h.z};   // the host sweep's sort key: lo + hi, ties by index (the sort is stable)
+    for (int a = 0; a < 3; a++) { keys[(size_t)a * n + i] = f2ord(c[a] + 0.0f); vals[(size_t)a * n + i] = i; }   // + 0: -0 and +0 tie, as they compare
+}
+
+__global__ void k_sah_init(SahArgs A) {
+    SahCtl* c = A.ctl;
+    for (int i = threadIdx.x; i < SAH_MAX_LEVELS + 2; i += blockDim.x) { c->nseg[i] = 0; c->cursor[i] = 0; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        c->depth = 0; c->too_deep = 0; c->area_sum = 0.0;
+        c->nseg[0] = 1;
+        A.queue[0][0] = SahSeg{0u, A.n, 0, 0u};
+    }
+}
+
+// exclusive block scan of one box per thread (union); `total` = union over the block.  s_w: [SAH_WARPS] scratch.
+__device__ __forceinline__ B6 sah_block_scan(const B6& v, B6& total, B6* s_w) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    B6 inc = v;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const B6 y = b6_shfl_up(inc, o); if (lane >= o) inc = b6_unite(inc, y); }
+    if (lane == 31) s_w[warp] = inc;
+    B6 ex = b6_shfl_up(inc, 1);
+    if (lane == 0) ex = b6_empty();
+    __syncthreads();
+    B6 pre = b6_empty();
+    total = b6_empty();
+    #pragma unroll
+    for (int w = 0; w < SAH_WARPS; w++) { const B6 t = s_w[w]; if (w < warp) pre = b6_unite(pre, t); total = b6_unite(total, t); }
+    __syncthreads();
+    return b6_unite(pre, ex);
+}
+
+__device__ __forceinline__ uint32_t sah_block_scan_u32(uint32_t v, uint32_t& total, uint32_t* s_w) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    uint32_t pre = 0;
+    total = 0;
+    #pragma unroll
+    for (int w = 0; w < SAH_WARPS; w++) { const uint32_t t = s_w[w]; if (w < warp) pre += t; total += t; }
+    __syncthreads();
+    return pre + inc - v;
+}
+
+__device__ __forceinline__ B6 sah_leaf_box(const SahArgs& A, uint32_t leaf) {
+    const float4 l = A.lo[leaf], h = A.hi[leaf];
+    return B6{l.x, l.y, l.z, h.x, h.y, h.z};
+}
+
+// One sweep over the segment `ids[0..count)` in chunks of SAH_CHUNK; FORWARD: element e = 0, 1, ...; else e = count - 1,
+// count - 2, ...  `visit(e, box)` sees the union of the elements swept so far, e included.
+template <bool FORWARD, class Visit>
+__device__ __forceinline__ void sah_sweep(const SahArgs& A, const uint32_t* ids, uint32_t count, B6* s_w, Visit&& visit) {
+    B6 carry = b6_empty();
+    for (uint32_t c0 = 0; c0 < count; c0 += SAH_CHUNK) {
+        B6 loc[SAH_ITEMS];
+        B6 run = b6_empty();
+        #pragma unroll
+        for (int k = 0; k < SAH_ITEMS; k++) {
+            const uint32_t s = c0 + threadIdx.x * SAH_ITEMS + k;          // sweep step
+            if (s < count) run = b6_unite(run, sah_leaf_box(A, ids[FORWARD ? s : count - 1 - s]));
+            loc[k] = run;
+        }
+        B6 total;
+        const B6 before = b6_unite(carry, sah_block_scan(run, total, s_w));
+        #pragma unroll
+        for (int k = 0; k < SAH_ITEMS; k++) {
+            const uint32_t s = c0 + threadIdx.x * SAH_ITEMS + k;
+            if (s < count) visit(FORWARD ? s : count - 1 - s, b6_unite(before, loc[k]));
+        }
+        carry = b6_unite(carry, total);
+    }
+}
+
+__global__ void __launch_bounds__(SAH_THREADS) k_sah_level(SahArgs A, uint32_t level) {
+    __shared__ B6 s_w[SAH_WARPS];
+    __shared__ B6 s_lr[SAH_WARPS][2];
+    __shared__ uint32_t s_u[SAH_WARPS];
+    __shared__ float s_cost[SAH_WARPS];
+    __shared__ uint32_t s_key[SAH_WARPS];
+    __shared__ uint32_t s_claim, s_best;
+    SahCtl* ctl = A.ctl;
+    const uint32_t nseg = ctl->nseg[level];
+    const SahSeg* in = A.queue[level & 1];
+    SahSeg* out = A.queue[(level & 1) ^ 1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (;;) {
+        if (threadIdx.x == 0) s_claim = atomicAdd(&ctl->cursor[level], 1u);
+        __syncthreads();
+        const uint32_t si = s_claim;
+        if (si >= nseg) return;
+        const SahSeg seg = in[si];
+        const uint32_t first = seg.first, count = seg.count;
+        float* ra = A.right_area + first;
+
+        // ---- score every split of every axis
+        float best = INFINITY;
+        uint32_t best_key = 0xffffffffu;                       // axis << 30 | split
+        for (uint32_t axis = 0; axis < 3; axis++) {
+            const uint32_t* ids = A.order[axis] + first;
+            sah_sweep<false>(A, ids, count, s_w, [&](uint32_t e, const B6& b) { if (e) ra[e] = b6_half_area(b); });   // area of [e, count)
+            __syncthreads();
+            sah_sweep<true>(A, ids, count, s_w, [&](uint32_t e, const B6& b) {
+                const uint32_t i = e + 1;                          // split after element e: |L| = i
+                if (i < count) {
+                    const float cost = b6_half_area(b) * (float)i + ra[i] * (float)(count - i);
+                    if (cost < best) { best = cost; best_key = axis << 30 | i; }
+                }
+            });
+            __syncthreads();
+        }
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float oc = __shfl_xor_sync(0xffffffffu, best, o);
+            const uint32_t ok = __shfl_xor_sync(0xffffffffu, best_key, o);
+            if (oc < best || (oc == best && ok < best_key)) { best = oc; best_key = ok; }
+        }
+        if (lane == 0) { s_cost[warp] = best; s_key[warp] = best_key; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float c = s_cost[0]; uint32_t k = s_key[0];
+            for (int w = 1; w < SAH_WARPS; w++) if (s_cost[w] < c || (s_cost[w] == c && s_key[w] < k)) { c = s_cost[w]; k = s_key[w]; }
+            if (k == 0xffffffffu) k = count / 2;               // no finite cost anywhere: the middle of the x order
+            s_best = k;
+        }
+        __syncthreads();
+        const uint32_t best_axis = s_best >> 30, split = s_best & 0x3fffffffu;
+
+        // ---- partition the other two orders (stable), boxes of both sides
+        const uint32_t* bid = A.order[best_axis] + first;
+        B6 bl = b6_empty(), br = b6_empty();
+        for (uint32_t i = threadIdx.x; i < count; i += SAH_THREADS) {
+            const uint32_t leaf = bid[i];
+            const bool right = i >= split;
+            A.goes_right[leaf] = right;
+            const B6 b = sah_leaf_box(A, leaf);
+            if (right) br = b6_unite(br, b); else bl = b6_unite(bl, b);
+        }
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { bl = b6_unite(bl, b6_shfl_xor(bl, o)); br = b6_unite(br, b6_shfl_xor(br, o)); }
+        if (lane == 0) { s_lr[warp][0] = bl; s_lr[warp][1] = br; }
+        __syncthreads();
+        for (uint32_t axis = 0; axis < 3; axis++) {
+            if (axis == best_axis) continue;
+            uint32_t* ids = A.order[axis] + first;
+            uint32_t* tmp = A.scratch + first;
+            uint32_t lefts_before = 0;                          // block-uniform carry
+            for (uint32_t c0 = 0; c0 < count; c0 += SAH_CHUNK) {
+                uint32_t id[SAH_ITEMS], nl = 0;
+                bool r[SAH_ITEMS];
+                #pragma unroll
+                for (int k = 0; k < SAH_ITEMS; k++) {
+                    const uint32_t i = c0 + threadIdx.x * SAH_ITEMS + k;
+                    id[k] = i < count ? ids[i] : 0u;
+                    r[k] = i < count ? A.goes_right[id[k]] != 0 : true;
+                    nl += r[k] ? 0u : 1u;
+                }
+                uint32_t total;
+                uint32_t l = lefts_before + sah_block_scan_u32(nl, total, s_u);
+                #pragma unroll
+                for (int k = 0; k < SAH_ITEMS; k++) {
+                    const uint32_t i = c0 + threadIdx.x * SAH_ITEMS + k;
+                    if (i < count) { tmp[r[k] ? split + (i - l) : l] = id[k]; l += r[k] ? 0u : 1u; }
+                }
+                lefts_before += total;
+            }
+            __syncthreads();
+            for (uint32_t i = threadIdx.x; i < count; i += SAH_THREADS) ids[i] = tmp[i];
+            __syncthreads();
+        }
+
+        // ---- the node, and its children into the next level's queue
+        if (threadIdx.x == 0) {
+            B6 L = s_lr[0][0], R = s_lr[0][1];
+            for (int w = 1; w < SAH_WARPS; w++) { L = b6_unite(L, s_lr[w][0]); R = b6_unite(R, s_lr[w][1]); }
+            const uint32_t nl = split, nr = count - split;
+            int c0, c1;
+            uint32_t leaf_depth = 0;
+            SahSeg kids[2];
+            uint32_t nk = 0;
+            if (nl == 1) {
+                const uint32_t leaf = bid[0];
+                c0 = A.leaf_code ? A.leaf_code[leaf] : ~(int)leaf;
+                leaf_depth = max(leaf_depth, seg.level + 1 + (A.has_depth ? (uint32_t)A.lo[leaf].w : 0u));
+            } else { c0 = seg.me + 1; kids[nk++] = SahSeg{first, nl, seg.me + 1, seg.level + 1}; }
+            if (nr == 1) {
+                const uint32_t leaf = bid[split];
+                c1 = A.leaf_code ? A.leaf_code[leaf] : ~(int)leaf;
+                leaf_depth = max(leaf_depth, seg.level + 1 + (A.has_depth ? (uint32_t)A.lo[leaf].w : 0u));
+            } else { c1 = seg.me + (int)split; kids[nk++] = SahSeg{first + split, nr, seg.me + (int)split, seg.level + 1}; }
+            BNode nd;
+            nd.n0 = make_float4(L.lx, L.hx, L.ly, L.hy);
+            nd.n1 = make_float4(R.lx, R.hx, R.ly, R.hy);
+            nd.n2 = make_float4(L.lz, L.hz, R.lz, R.hz);
+            nd.child0 = c0; nd.child1 = c1; nd.pad0 = 0; nd.pad1 = 0;
+            A.nodes[seg.me] = nd;
+            const B6 u = b6_unite(L, R);
+            atomicAdd(&ctl->area_sum, (double)b6_half_area(u));
+            if (leaf_depth) atomicMax(&ctl->depth, leaf_depth);
+            if (seg.level == 0) { ctl->root_lo[0] = u.lx; ctl->root_lo[1] = u.ly; ctl->root_lo[2] = u.lz; ctl->root_hi[0] = u.hx; ctl->root_hi[1] = u.hy; ctl->root_hi[2] = u.hz; }
+            if (nk) {
+                if (seg.level + 3 > RT_STACK_DEPTH) ctl->too_deep = 1;   // a degenerate chain: the caller discards the tree
+                else {
+                    const uint32_t at = atomicAdd(&ctl->nseg[level + 1], nk);
+                    for (uint32_t k = 0; k < nk; k++) out[at + k] = kids[k];
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// bump allocator over DeviceScene::scratch; pass 1 (base == nullptr) only measures
+struct Arena {
+    char* base; size_t off = 0;
+    explicit Arena(void* b) : base((char*)b) {}
+    template <class T> T* take(size_t count) {
+        off = (off + 255) & ~size_t(255);
+        T* p = base ? (T*)(base + off) : nullptr;
+        off += (count ? count : 1) * sizeof(T);
+        return p;
+    }
+};
 
 } // namespace
 
-int compute_medium_bounds(DeviceScene& ds, float time_lo, float time_hi, cudaStream_t stream) {
+int compute_medium_bounds(DeviceScene& ds, DMedium* media, float time_lo, float time_hi, cudaStream_t stream) {
     if (!ds.view.n_media) return RT_OK;
-    k_medium_bounds<<<(ds.view.n_media + 63) / 64, 64, 0, stream>>>(ds.view, (DMedium*)ds.d_media, ds.view.n_media, time_lo, time_hi);
+    k_medium_bounds<<<(ds.view.n_media + 63) / 64, 64, 0, stream>>>(ds.view, media, ds.view.n_media, time_lo, time_hi);
     RT_CUDA(cudaGetLastError());
-    RT_CUDA(cudaStreamSynchronize(stream));
     return RT_OK;
 }
 
-// ---- host full-sweep SAH build (small scenes) -----------------------------------------------------------------------
-// Top-down, one primitive per leaf: at every node every split position along every axis (primitives ordered by box
-// centre) is scored with area(L) * |L| + area(R) * |R| and the best of the 3 x (n - 1) candidates wins.  The three
-// orders are sorted ONCE; a split stably partitions the other two, so a level costs O(n) and the build O(n log n) on one
-// host thread: 6 ms for the 3407 primitives of the Next-Week final scene.  Against PLOC it saves 13 % of the node visits
-// per ray there (18.3 -> 15.9; extend -16 %), which is why scenes up to RT_SAH_MAX primitives take this path; PLOC
-// stays for everything larger (1 M triangles in 4 ms on the GPU).
-// Input: boxes in leaf (sorted) order; output: nodes numbered from the top, root = 0.
+// ---- host full-sweep SAH build: round 1's default, now the checker of the GPU sweep (RT_BUILD_HOST_SAH) ---------------
+// The same algorithm, sequential per subtree; up to 16 host threads near the top.
+// Input: boxes in leaf (sorted) order; output: nodes numbered in preorder, root = 0.
 namespace {
 struct HostBox { float lo[3], hi[3]; };
 inline void grow(HostBox& b, const HostBox& o) { for (int a = 0; a < 3; a++) { b.lo[a] = std::min(b.lo[a], o.lo[a]); b.hi[a] = std::max(b.hi[a], o.hi[a]); } }
@@ -590,12 +879,9 @@ struct SahBuilder {
     std::vector<BNode> nodes;                  // preorder: a subtree over k primitives owns k - 1 consecutive nodes, so subtrees
                                                // can be built by different threads without sharing anything but disjoint ranges
     struct Result { HostBox box; int code; double area_sum; uint32_t depth; };
-    const int* leaf_code = nullptr;            // child code of leaf i (default ~i: primitive i)
-    const uint32_t* leaf_depth = nullptr;      // depth of the subtree hanging below leaf i (default 0)
 
-    explicit SahBuilder(const std::vector<HostBox>& l, const int* codes = nullptr, const uint32_t* depths = nullptr)
-        : leaf(l), scratch(l.size()), goes_right(l.size()), right_area(l.size()), nodes(l.size() > 1 ? l.size() - 1 : 1),
-          leaf_code(codes), leaf_depth(depths) {
+    explicit SahBuilder(const std::vector<HostBox>& l)
+        : leaf(l), scratch(l.size()), goes_right(l.size()), right_area(l.size()), nodes(l.size() > 1 ? l.size() - 1 : 1) {
         std::thread sorters[3];
         for (int axis = 0; axis < 3; axis++)
             sorters[axis] = std::thread([this, axis]() {
@@ -613,7 +899,7 @@ struct SahBuilder {
     Result build(size_t first, size_t count, int me, uint32_t level) {
         if (count == 1 || level + 2 > RT_STACK_DEPTH) { // (too deep for the traversal stack: the caller discards the tree)
             const uint32_t i = order[0][first];
-            return Result{leaf[i], leaf_code ? leaf_code[i] : ~(int)i, 0.0, level + (leaf_depth ? leaf_depth[i] : 0u)};
+            return Result{leaf[i], ~(int)i, 0.0, level};
         }
         float best = INFINITY; int best_axis = 0; size_t best_split = count / 2;
         float* ra = right_area.data() + first;
@@ -661,210 +947,59 @@ struct SahBuilder {
 };
 constexpr uint32_t SAH_MAX_DEFAULT = 65536;
 constexpr int PLOC_TOP_DEFAULT = 32768;       // clusters left when PLOC hands the top of the tree to the SAH sweep
-} // namespace
 
-int build_lbvh(DeviceScene& ds, const DPrim* d_prims_in, const uint32_t* d_leaf_ids_in, uint32_t n, float time_lo, float time_hi,
-               cudaStream_t stream) {
-    if (n == 0) return RT_OK;
-    cudaEvent_t ev[6];
-    for (auto& e : ev) RT_CUDA(cudaEventCreate(&e));
+struct SahScratch {      // carved from the build arena
+    uint64_t *keys_a, *keys_b;
+    uint32_t *vals_a, *vals_b, *counts, *trivial, *scratch;
+    uint8_t* goes_right;
+    float* right_area;
+    SahSeg* queue[2];
+    SahCtl* ctl;
+};
+SahScratch carve_sah(Arena& ar, uint32_t n) {
+    SahScratch s;
     const uint32_t nblocks = (n + SORT_TILE - 1) / SORT_TILE;
-    const uint32_t tb = 256, gb = (n + tb - 1) / tb;
+    s.keys_a = ar.take<uint64_t>(3 * (size_t)n); s.keys_b = ar.take<uint64_t>(3 * (size_t)n);
+    s.vals_a = ar.take<uint32_t>(3 * (size_t)n); s.vals_b = ar.take<uint32_t>(3 * (size_t)n);
+    s.counts = ar.take<uint32_t>(3 * (size_t)256 * nblocks); s.trivial = ar.take<uint32_t>(4);
+    s.scratch = ar.take<uint32_t>(n); s.goes_right = ar.take<uint8_t>(n); s.right_area = ar.take<float>(n);
+    s.queue[0] = ar.take<SahSeg>(n / 2 + 2); s.queue[1] = ar.take<SahSeg>(n / 2 + 2);
+    s.ctl = ar.take<SahCtl>(1);
+    return s;
+}
 
-    float4 *box_lo = nullptr, *box_hi = nullptr, *leaf_lo = nullptr, *leaf_hi = nullptr, *node_lo = nullptr, *node_hi = nullptr;
-    uint64_t *keys_a = nullptr, *keys_b = nullptr;
-    uint32_t *vals_a = nullptr, *vals_b = nullptr, *counts = nullptr, *scene_ord = nullptr, *trivial = nullptr, *visit = nullptr;
-    int *left = nullptr, *right = nullptr, *parent_internal = nullptr, *parent_leaf = nullptr;
-    RT_CUDA(dalloc(&box_lo, n)); RT_CUDA(dalloc(&box_hi, n)); RT_CUDA(dalloc(&leaf_lo, n)); RT_CUDA(dalloc(&leaf_hi, n));
-    RT_CUDA(dalloc(&node_lo, n)); RT_CUDA(dalloc(&node_hi, n));
-    RT_CUDA(dalloc(&keys_a, n)); RT_CUDA(dalloc(&keys_b, n)); RT_CUDA(dalloc(&vals_a, n)); RT_CUDA(dalloc(&vals_b, n));
-    RT_CUDA(dalloc(&counts, (size_t)256 * nblocks)); RT_CUDA(dalloc(&scene_ord, 6)); RT_CUDA(dalloc(&trivial, 1)); RT_CUDA(dalloc(&visit, n));
-    RT_CUDA(dalloc(&left, n)); RT_CUDA(dalloc(&right, n)); RT_CUDA(dalloc(&parent_internal, n)); RT_CUDA(dalloc(&parent_leaf, n));
-
-    DPrim* prims_out = nullptr; uint32_t* leaf_ids_out = nullptr; BNode* nodes = nullptr;
-    RT_CUDA(dalloc(&prims_out, n)); RT_CUDA(dalloc(&leaf_ids_out, n));
-    const uint32_t n_nodes = n > 1 ? n - 1 : 1;
-    RT_CUDA(dalloc(&nodes, n_nodes));
-
-    const uint32_t ord_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
-    RT_CUDA(cudaMemcpyAsync(scene_ord, ord_init, sizeof(ord_init), cudaMemcpyHostToDevice, stream));
-    RT_CUDA(cudaMemsetAsync(visit, 0, sizeof(uint32_t) * n, stream));
-
-    RT_CUDA(cudaEventRecord(ev[0], stream));
-    k_prim_bounds<<<gb, tb, 0, stream>>>(ds.view, d_prims_in, n, time_lo, time_hi, box_lo, box_hi, scene_ord);
-    k_morton<<<gb, tb, 0, stream>>>(box_lo, box_hi, n, scene_ord, keys_a, vals_a);
-    RT_CUDA(cudaEventRecord(ev[1], stream));
-    uint64_t *kin = keys_a, *kout = keys_b;
-    uint32_t *vin = vals_a, *vout = vals_b;
-    for (int pass = 0; pass < 8; pass++) {   // 63-bit codes: 8 passes of 8 bits
-        const int shift = 8 * pass;
-        k_sort_hist<<<nblocks, SORT_THREADS, 0, stream>>>(kin, n, shift, counts);
-        k_sort_scan<<<1, 1024, 0, stream>>>(counts, 256 * nblocks, nblocks, n, trivial);
-        k_sort_scatter<<<nblocks, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, counts, trivial);
+// Queues the whole sweep on `stream` (no synchronisation): leaves (lo, hi[, codes, depths in lo.w]) -> nodes[0 .. n - 2].
+// The caller reads *ctl afterwards.  `levels_out`: how many level launches were queued.
+int sah_sweep_gpu(const SahScratch& S, const float4* lo, const float4* hi, const int* codes, bool has_depth, uint32_t n, BNode* nodes,
+                  int sms, cudaStream_t stream, uint32_t* levels_out) {
+    const uint32_t nblocks = (n + SORT_TILE - 1) / SORT_TILE, gb = (n + 255) / 256;
+    k_sah_keys<<<gb, 256, 0, stream>>>(lo, hi, n, S.keys_a, S.vals_a);
+    uint64_t *kin = S.keys_a, *kout = S.keys_b;
+    uint32_t *vin = S.vals_a, *vout = S.vals_b;
+    for (int pass = 0; pass < 4; pass++) {   // 32-bit keys; the sort is stable, so equal centres keep index order
+        k_sort_hist<<<dim3(nblocks, 3), SORT_THREADS, 0, stream>>>(kin, n, 8 * pass, S.counts);
+        k_sort_scan<<<dim3(1, 3), 1024, 0, stream>>>(S.counts, 256 * nblocks, nblocks, n, S.trivial);
+        k_sort_scatter<<<dim3(nblocks, 3), SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, 8 * pass, S.counts, S.trivial);
         std::swap(kin, kout); std::swap(vin, vout);
     }
-    RT_CUDA(cudaEventRecord(ev[2], stream));
-    const char* which = getenv("RT_BVH");
-    const bool use_karras = n == 1 || (which && !strcmp(which, "karras"));   // RT_BVH=karras: the Morton-prefix hierarchy (A/B)
-    const uint32_t sah_max = getenv("RT_SAH_MAX") ? (uint32_t)atoi(getenv("RT_SAH_MAX")) : SAH_MAX_DEFAULT;
-    const bool use_sah = !use_karras && (which ? !strcmp(which, "sah") : n <= sah_max);   // RT_BVH=sah|ploc|karras forces one builder
-    bool sah_built = false;
-    if (use_sah) {
-        std::vector<float4> h_lo(n), h_hi(n);
-        std::vector<uint32_t> h_ord(n);
-        RT_CUDA(cudaMemcpyAsync(h_lo.data(), box_lo, sizeof(float4) * n, cudaMemcpyDeviceToHost, stream));
-        RT_CUDA(cudaMemcpyAsync(h_hi.data(), box_hi, sizeof(float4) * n, cudaMemcpyDeviceToHost, stream));
-        RT_CUDA(cudaMemcpyAsync(h_ord.data(), vin, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, stream));
-        RT_CUDA(cudaStreamSynchronize(stream));
-        std::vector<HostBox> leaf(n);
-        for (uint32_t i = 0; i < n; i++) {
-            const float4 l = h_lo[h_ord[i]], h = h_hi[h_ord[i]];
-            leaf[i] = HostBox{{l.x, l.y, l.z}, {h.x, h.y, h.z}};
-        }
-        SahBuilder b(leaf);
-        const SahBuilder::Result root = b.build(0, n, 0, 0);
-        if (root.depth + 2 <= RT_STACK_DEPTH) {         // else: a degenerate chain — PLOC below takes over
-            RT_CUDA(cudaMemcpyAsync(nodes, b.nodes.data(), sizeof(BNode) * n_nodes, cudaMemcpyHostToDevice, stream));
-            RT_CUDA(cudaStreamSynchronize(stream));
-            RT_CUDA(cudaEventRecord(ev[3], stream));
-            RT_CUDA(cudaEventRecord(ev[4], stream));
-            ds.build.bvh_depth = root.depth;
-            ds.build.sah_internal = (float)(root.area_sum / std::max(half_area(root.box), 1e-30f));
-            ds.build.build_rounds = 0; ds.build.ploc_radius = 0; ds.build.builder = RT_BUILDER_HOST_SAH;
-            sah_built = true;
-        }
+    SahArgs A;
+    A.lo = lo; A.hi = hi; A.leaf_code = codes; A.has_depth = has_depth ? 1 : 0;
+    for (int a = 0; a < 3; a++) A.order[a] = vin + (size_t)a * n;
+    A.scratch = S.scratch; A.goes_right = S.goes_right; A.right_area = S.right_area;
+    A.queue[0] = S.queue[0]; A.queue[1] = S.queue[1]; A.ctl = S.ctl; A.nodes = nodes; A.n = n;
+    k_sah_init<<<1, 128, 0, stream>>>(A);
+    // Level l holds at most min(2^l, n / 2) segments; SAH trees of real scenes are 1.5-2.5 x log2(n) deep.  Launches beyond the
+    // last level find an empty queue and exit; a tree deeper than what is queued here is caught by the caller's check.
+    uint32_t log2n = 0;
+    while ((1u << log2n) < n) log2n++;
+    const uint32_t levels = std::min<uint32_t>(SAH_MAX_LEVELS, 3 * log2n + 8);
+    for (uint32_t l = 0; l < levels; l++) {
+        const uint32_t cap = l < 31 ? std::min<uint32_t>(1u << l, n / 2 + 1) : n / 2 + 1;
+        k_sah_level<<<std::min<uint32_t>(cap, (uint32_t)sms * 8u), SAH_THREADS, 0, stream>>>(A, l);
     }
-    if (sah_built) {
-        // nodes are in place
-    } else if (use_karras) {
-        ds.build.builder = RT_BUILDER_KARRAS;
-        if (n > 1) k_karras<<<gb, tb, 0, stream>>>(kin, (int)n, left, right, parent_internal, parent_leaf);
-        RT_CUDA(cudaEventRecord(ev[3], stream));
-        k_refit<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, right, parent_internal, parent_leaf, leaf_lo, leaf_hi, node_lo, node_hi, visit);
-        RT_CUDA(cudaEventRecord(ev[4], stream));
-        k_emit_nodes<<<gb, tb, 0, stream>>>((int)n, left, right, leaf_lo, leaf_hi, node_lo, node_hi, nodes);
-    } else {
-        // PLOC: cluster lists ping-pong between (cid_a, leaf_*) and (cid_b, node_*); `left`/`right` double as cid arrays,
-        // `parent_internal` as the nearest-neighbour array.  The search radius trades differently per scene (flat rect
-        // soups like a wide window less than triangle meshes do), and a build is ~1 ms per 250 k primitives, so scenes up
-        // to PLOC_SWEEP_MAX primitives are built with several radii and the tree with the smallest summed internal-node
-        // area (the SAH traversal term) is kept; measured node visits per ray follow that sum (profiles/r01_v5_ploc.md).
-        unsigned long long *scan_local = nullptr, *scan_sums = nullptr;
-        float* area_sum = nullptr;
-        BNode* nodes_alt = nullptr;
-        RT_CUDA(dalloc(&area_sum, 1));
-        const int max_sblk = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
-        RT_CUDA(dalloc(&scan_local, n)); RT_CUDA(dalloc(&scan_sums, (size_t)max_sblk + 1));
-        RT_CUDA(cudaEventRecord(ev[3], stream));
-        const char* rad = getenv("RT_PLOC_RADIUS");
-        std::vector<int> radii;
-        if (rad) radii.push_back(std::min(PLOC_MAX_RADIUS, std::max(1, atoi(rad))));
-        else if (n <= PLOC_SWEEP_MAX) radii = {4, 8, 16, 32};
-        else radii = {16};
-        if (radii.size() > 1) RT_CUDA(dalloc(&nodes_alt, n_nodes));
-        const int total_internal = (int)n - 1;
-        float best_area = INFINITY;
-        BNode* best_nodes = nullptr;
-        for (const int radius : radii) {
-            BNode* target = best_nodes == nodes ? nodes_alt : nodes;          // never overwrite the best tree so far
-            int *cid_in = left, *cid_out = right, *nn = parent_internal;
-            float4 *lo_in = leaf_lo, *hi_in = leaf_hi, *lo_out = node_lo, *hi_out = node_hi;
-            RT_CUDA(cudaMemsetAsync(area_sum, 0, sizeof(float), stream));
-            k_ploc_init<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, cid_in, lo_in, hi_in);
-            int cur_n = (int)n, created = 0, rounds = 0;
-            // Hybrid: agglomeration stops once at most `top_n` clusters are left and the TOP of the tree — the levels every
-            // ray walks, and where bounded-radius clustering is weakest — is built over the cluster boxes by the host SAH
-            // sweep (1-2 ms).  PLOC numbers its nodes from the high indices down, so the top nodes get [0, clusters - 1).
-            // 1 M triangles: 26.7 -> 24.4 node visits per ray, extend -8 %, build +5 ms (top of 32 k clusters; 25.0 with 2 k).
-            // Scenes below 16 k primitives — PLOC only when forced by RT_BVH=ploc — stay pure PLOC for A/B.
-            const int top_want = getenv("RT_PLOC_TOP") ? std::max(1, atoi(getenv("RT_PLOC_TOP"))) : PLOC_TOP_DEFAULT;
-            const int top_n = n >= 16384u ? std::min<int>(top_want, (int)(n / 8u)) : 1;
-            while (cur_n > top_n) {
-                const int nblk = (cur_n + PLOC_BLOCK - 1) / PLOC_BLOCK, sblk = (cur_n + SCAN_TILE - 1) / SCAN_TILE;
-                k_ploc_nn<<<nblk, PLOC_BLOCK, 0, stream>>>(lo_in, hi_in, cur_n, nn, radius);
-                k_ploc_scan_block<<<sblk, PLOC_BLOCK, 0, stream>>>(nn, cur_n, scan_local, scan_sums);
-                k_ploc_scan_sums<<<1, 1024, 0, stream>>>(scan_sums, sblk);
-                k_ploc_merge<<<nblk, PLOC_BLOCK, 0, stream>>>(nn, cur_n, scan_local, scan_sums, cid_in, lo_in, hi_in, cid_out, lo_out, hi_out, target,
-                                                              total_internal - 1 - created, area_sum);
-                unsigned long long tot = 0;
-                RT_CUDA(cudaMemcpyAsync(&tot, scan_sums + sblk, sizeof(tot), cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaStreamSynchronize(stream));
-                const int survivors = (int)(uint32_t)tot, merges = (int)(tot >> 32);
-                if (merges <= 0 || survivors != cur_n - merges) { set_error("bvh build: PLOC round made no progress (internal error)"); return RT_ERR_STATE; }
-                cur_n = survivors; created += merges; rounds++;
-                std::swap(cid_in, cid_out); std::swap(lo_in, lo_out); std::swap(hi_in, hi_out);
-            }
-            if (created + cur_n - 1 != total_internal) { set_error("bvh build: PLOC node count mismatch (internal error)"); return RT_ERR_STATE; }
-            float4 root_lo, root_hi;
-            float h_area = 0.f;
-            uint32_t depth = 0;
-            if (cur_n > 1) {   // top of the tree over the remaining clusters
-                std::vector<float4> c_lo(cur_n), c_hi(cur_n);
-                std::vector<int> c_id(cur_n);
-                RT_CUDA(cudaMemcpyAsync(c_lo.data(), lo_in, sizeof(float4) * cur_n, cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaMemcpyAsync(c_hi.data(), hi_in, sizeof(float4) * cur_n, cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaMemcpyAsync(c_id.data(), cid_in, sizeof(int) * cur_n, cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaMemcpyAsync(&h_area, area_sum, sizeof(float), cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaStreamSynchronize(stream));
-                std::vector<HostBox> cl(cur_n);
-                std::vector<uint32_t> cl_depth(cur_n);
-                for (int i = 0; i < cur_n; i++) {
-                    cl[i] = HostBox{{c_lo[i].x, c_lo[i].y, c_lo[i].z}, {c_hi[i].x, c_hi[i].y, c_hi[i].z}};
-                    cl_depth[i] = (uint32_t)c_lo[i].w;
-                }
-                SahBuilder top(cl, c_id.data(), cl_depth.data());
-                const SahBuilder::Result r = top.build(0, (size_t)cur_n, 0, 0);
-                RT_CUDA(cudaMemcpyAsync(target, top.nodes.data(), sizeof(BNode) * (cur_n - 1), cudaMemcpyHostToDevice, stream));
-                RT_CUDA(cudaStreamSynchronize(stream));
-                root_lo = make_float4(r.box.lo[0], r.box.lo[1], r.box.lo[2], 0.f);
-                root_hi = make_float4(r.box.hi[0], r.box.hi[1], r.box.hi[2], 0.f);
-                h_area += (float)r.area_sum;
-                depth = r.depth;
-            } else {
-                RT_CUDA(cudaMemcpyAsync(&root_lo, lo_in, sizeof(float4), cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaMemcpyAsync(&root_hi, hi_in, sizeof(float4), cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaMemcpyAsync(&h_area, area_sum, sizeof(float), cudaMemcpyDeviceToHost, stream));
-                RT_CUDA(cudaStreamSynchronize(stream));
-                depth = (uint32_t)root_lo.w;
-            }
-            if (depth + 2 > RT_STACK_DEPTH) continue;                         // deeper than the traversal stack: not a candidate
-            if (h_area < best_area) {
-                best_area = h_area; best_nodes = target;
-                const float rdx = root_hi.x - root_lo.x, rdy = root_hi.y - root_lo.y, rdz = root_hi.z - root_lo.z;
-                ds.build.bvh_depth = depth;
-                ds.build.sah_internal = h_area / fmaxf(rdx * rdy + rdy * rdz + rdz * rdx, 1e-30f);
-                ds.build.build_rounds = (uint32_t)rounds;
-                ds.build.ploc_radius = (uint32_t)radius;
-                ds.build.builder = RT_BUILDER_PLOC;
-            }
-        }
-        cudaFree(scan_local); cudaFree(scan_sums); cudaFree(area_sum);
-        if (!best_nodes) { cudaFree(nodes_alt); set_error("bvh build: tree deeper than the traversal stack; rebuild with RT_BVH=karras"); return RT_ERR_UNSUPPORTED; }
-        if (best_nodes == nodes_alt) std::swap(nodes, nodes_alt);
-        cudaFree(nodes_alt);
-        RT_CUDA(cudaEventRecord(ev[4], stream));
-    }
-    k_permute_prims<<<gb, tb, 0, stream>>>(n, vin, d_prims_in, d_leaf_ids_in, prims_out, leaf_ids_out);
-    RT_CUDA(cudaEventRecord(ev[5], stream));
     RT_CUDA(cudaGetLastError());
-    RT_CUDA(cudaStreamSynchronize(stream));
-
-    cudaEventElapsedTime(&ds.build.ms_morton, ev[0], ev[1]);
-    cudaEventElapsedTime(&ds.build.ms_sort, ev[1], ev[2]);
-    cudaEventElapsedTime(&ds.build.ms_hierarchy, ev[2], ev[3]);
-    cudaEventElapsedTime(&ds.build.ms_refit, ev[3], ev[4]);
-    cudaEventElapsedTime(&ds.build.ms_collapse, ev[4], ev[5]);
-    for (auto& e : ev) cudaEventDestroy(e);
-
-    ds.d_prims = prims_out; ds.d_prim_leaf_id = leaf_ids_out; ds.d_nodes = nodes;
-    ds.view.prims = prims_out; ds.view.prim_leaf_id = leaf_ids_out; ds.view.nodes = nodes;
-    ds.view.n_nodes = n_nodes;
-    ds.build.n_nodes = n_nodes;
-
-    cudaFree(box_lo); cudaFree(box_hi); cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(node_lo); cudaFree(node_hi);
-    cudaFree(keys_a); cudaFree(keys_b); cudaFree(vals_a); cudaFree(vals_b); cudaFree(counts); cudaFree(scene_ord);
-    cudaFree(trivial); cudaFree(visit); cudaFree(left); cudaFree(right); cudaFree(parent_internal); cudaFree(parent_leaf);
+    *levels_out = levels;
     return RT_OK;
 }
 
-} // namespace rtb
+} // namespace

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include "../../include/rt_b200.h"
 
@@ -75,20 +76,64 @@ struct SceneView {
     uint32_t semantics;            // rt_semantics bits (rt_b200.h); 0 = the reference's behaviour
 };
 
-#define RT_STACK_DEPTH 96   // traversal stack entries (traverse.cuh); Karras trees are bounded by key + index bits, PLOC trees are checked at build
+#define RT_STACK_DEPTH 96   // deepest binary tree the builders accept (a traversal stack never holds more entries than the tree has levels)
+
+// Grow-only device / pinned-host buffers: a re-commit of a scene reuses every allocation of the previous one
+// (cudaMalloc / cudaFree synchronise the device; round 1 paid ~40 of them per commit).
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        const size_t want = bytes + bytes / 4 + 256;
+        const cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+struct PinnedBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        const cudaError_t e = cudaHostAlloc(&p, bytes + 256, cudaHostAllocDefault);
+        if (e == cudaSuccess) cap = bytes + 256;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+struct DeviceImage {
+    cudaArray_t array = nullptr;
+    cudaTextureObject_t tex = 0;
+    uint32_t width = 0, height = 0;
+};
 
 struct DeviceScene {
     int device = -1;
     SceneView view{};
-    // owned allocations
-    void* d_prims = nullptr; void* d_prim_leaf_id = nullptr; void* d_bprims = nullptr; void* d_media = nullptr;
-    void* d_tri_attrs = nullptr; void* d_xops = nullptr; void* d_chains = nullptr; void* d_materials = nullptr;
-    void* d_textures = nullptr; void* d_perlins = nullptr; void* d_images = nullptr; void* d_nodes = nullptr;
-    void* d_active_media = nullptr;
-    cudaArray_t* image_arrays = nullptr;
-    cudaTextureObject_t* image_objs = nullptr;
-    uint32_t n_images = 0;
+    // owned allocations, all grow-only and reused by the next commit on this device
+    DevBuf tables;        // every small table of the scene + the primitives in flatten order: ONE H2D copy per commit
+    DevBuf prims, prim_leaf_id, nodes, nodes_alt, wide;   // build outputs
+    DevBuf scratch;       // build arena
+    DevBuf query;         // rt_first_hit staging
+    DevBuf accum;         // rt_render's accumulation buffer
+    PinnedBuf staging;    // host image of `tables` (filled once per flattening)
+    PinnedBuf rgba;       // RGBA8 expansion of every image texture (filled once per flattening)
+    PinnedBuf readback;   // small results the host waits for (PLOC round totals, build control block)
+    std::vector<DeviceImage> images;
+    cudaEvent_t ev[10] = {};              // commit / build phase timers, created once
+    cudaStream_t stream = nullptr;        // commit stream (non-blocking)
+    uint64_t staged_generation = 0;       // FlatScene::generation the staging buffers were filled from
+    uint64_t committed_generation = 0;    // ... and the one the device copy describes (0 = none)
+    uint32_t committed_semantics = 0;
     rt_build_stats build{};
+    struct { uint32_t sah_levels = 0; const DPrim* prims_in = nullptr; const uint32_t* leaf_in = nullptr; uint32_t n = 0; float t_lo = 0, t_hi = 0; } pending;   // build_bvh -> build_bvh_finish
     struct RenderPool* pool = nullptr;   // wavefront state, created lazily by the renderer
 };
 
@@ -97,14 +142,20 @@ void set_error(const std::string& e);
 bool cuda_fail(cudaError_t e, const char* what, const char* file, int line);   // true (and sets error) on failure
 #define RT_CUDA(call) do { if (rtb::cuda_fail((call), #call, __FILE__, __LINE__)) return RT_ERR_CUDA; } while (0)
 
-// bvh_build.cu: builds the LBVH over `prims` (device, flatten order) and returns them reordered.
-int build_lbvh(DeviceScene& ds, const DPrim* d_prims_in, const uint32_t* d_leaf_ids_in, uint32_t n,
-               float time_lo, float time_hi, cudaStream_t stream);
+// bvh_build.cu: queues the build of the BVH over `prims` (device, flatten order) into ds.prims / ds.prim_leaf_id / ds.nodes.
+int build_bvh(DeviceScene& ds, const rt_build_settings& bs, const DPrim* d_prims_in, const uint32_t* d_leaf_ids_in, uint32_t n,
+              float time_lo, float time_hi, cudaStream_t stream);
+// bvh_build.cu: after the commit's one synchronisation — reads the build's control block, fills the statistics, and rebuilds
+// with PLOC in the one case the sweep gives up on (a degenerate chain deeper than RT_STACK_DEPTH)
+int build_bvh_finish(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t stream);
 
 // bvh_build.cu: fills DMedium::lo / hi of every medium (in place, device)
-int compute_medium_bounds(DeviceScene& ds, float time_lo, float time_hi, cudaStream_t stream);
+int compute_medium_bounds(DeviceScene& ds, DMedium* media, float time_lo, float time_hi, cudaStream_t stream);
 
 // wavefront.cu
 void render_pool_destroy(struct RenderPool* p);
+
+// device_api.cu: the scene's device copy, provided it describes the scene as it is now (RT_ERR_STATE otherwise)
+int device_scene_current(rt_scene* s, DeviceScene** out, const char* who);
 
 } // namespace rtb

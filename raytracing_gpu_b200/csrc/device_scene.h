@@ -13,5 +13,6 @@ void set_error(const std::string& e);
 HostScene& host_of(rt_scene* s);
 DeviceScene*& device_of(rt_scene* s);
 void device_scene_destroy(DeviceScene* d);
+bool device_scene_is_current(rt_scene* s);   // a device copy exists and describes the scene as recorded now
 
 } // namespace rtb

@@ -2,6 +2,7 @@
 // Compiled with -ffp-contract=off: the few float expressions here (camera, triangle setup) follow the
 // reference's expression order so the tables are bit-identical to what its constructors compute.
 #include "scene_host.h"
+#include <atomic>
 
 #include <cmath>
 #include <cstring>
@@ -185,6 +186,8 @@ int HostScene::flatten(std::string& err) {
     std::memcpy(h.background, background, sizeof(background));
     h.camera = camera;
     flat.valid = true;
+    static std::atomic<uint64_t> next_generation{1};
+    flat.generation = next_generation.fetch_add(1);
     return (int)fl.next_leaf;
 }
 

@@ -40,11 +40,7 @@ struct FlatScene {
     std::vector<rt_flat_image> images;
     std::vector<uint8_t> image_bytes;
     bool valid = false;
-    // filled by the first rt_scene_commit of this flattening and reused by later ones (a re-commit then only uploads and
-    // builds): the primitives as 48-byte device records, their leaf ids, the images expanded to RGBA8
-    mutable std::vector<uint8_t> commit_prims, commit_bprims;
-    mutable std::vector<uint32_t> commit_leaf_ids;
-    mutable std::vector<std::vector<uint8_t>> commit_rgba;
+    uint64_t generation = 0;   // unique per successful flatten(): the device copy records which flattening it describes
 };
 
 struct HostScene {
