@@ -1003,3 +1003,246 @@ int sah_sweep_gpu(const SahScratch& S, const float4* lo, const float4* hi, const
 }
 
 } // namespace
+
+int build_bvh(DeviceScene& ds, const rt_build_settings& bs, const DPrim* d_prims_in, const uint32_t* d_leaf_ids_in, uint32_t n,
+              float time_lo, float time_hi, cudaStream_t stream) {
+    ds.pending.sah_levels = 0; ds.pending.prims_in = d_prims_in; ds.pending.leaf_in = d_leaf_ids_in; ds.pending.n = n;
+    ds.pending.t_lo = time_lo; ds.pending.t_hi = time_hi;
+    if (n == 0) { ds.view.n_nodes = 0; ds.build.n_nodes = 0; return RT_OK; }
+    cudaEvent_t* ev = ds.ev + 2;   // [0], [1], [8] belong to commit_impl
+    const uint32_t nblocks = (n + SORT_TILE - 1) / SORT_TILE;
+    const uint32_t tb = 256, gb = (n + tb - 1) / tb;
+    const uint32_t n_nodes = n > 1 ? n - 1 : 1;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device);
+
+    // builder choice
+    const uint32_t sah_max = bs.sah_max_prims ? bs.sah_max_prims : SAH_MAX_DEFAULT;
+    uint32_t choice = bs.builder;
+    if (choice > RT_BUILD_GPU_SAH) { set_error("commit: unknown rt_build_settings::builder"); return RT_ERR_INVALID; }
+    if (choice == RT_BUILD_AUTO) choice = n <= sah_max ? RT_BUILD_GPU_SAH : RT_BUILD_PLOC;
+    if (n == 1) choice = RT_BUILD_KARRAS;
+
+    RT_CUDA(ds.prims.reserve(sizeof(DPrim) * (size_t)n));
+    RT_CUDA(ds.prim_leaf_id.reserve(sizeof(uint32_t) * (size_t)n));
+    RT_CUDA(ds.nodes.reserve(sizeof(BNode) * (size_t)n_nodes));
+    DPrim* prims_out = (DPrim*)ds.prims.p;
+    uint32_t* leaf_ids_out = (uint32_t*)ds.prim_leaf_id.p;
+    BNode* nodes = (BNode*)ds.nodes.p;
+
+    // scratch: measured first, then carved from the scene's grow-only arena
+    float4 *box_lo, *box_hi, *leaf_lo, *leaf_hi, *node_lo, *node_hi;
+    uint64_t *keys_a, *keys_b;
+    uint32_t *vals_a, *vals_b, *counts, *scene_ord, *trivial, *visit;
+    int *left, *right, *parent_internal, *parent_leaf;
+    unsigned long long *scan_local, *scan_sums;
+    float* area_sum;
+    SahScratch S{};
+    const int max_sblk = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+    const uint32_t ploc_top = bs.ploc_top ? bs.ploc_top : (uint32_t)PLOC_TOP_DEFAULT;
+    auto carve = [&](Arena& ar) {
+        box_lo = ar.take<float4>(n); box_hi = ar.take<float4>(n); leaf_lo = ar.take<float4>(n); leaf_hi = ar.take<float4>(n);
+        node_lo = ar.take<float4>(n); node_hi = ar.take<float4>(n);
+        keys_a = ar.take<uint64_t>(n); keys_b = ar.take<uint64_t>(n); vals_a = ar.take<uint32_t>(n); vals_b = ar.take<uint32_t>(n);
+        counts = ar.take<uint32_t>((size_t)256 * nblocks); scene_ord = ar.take<uint32_t>(8); trivial = ar.take<uint32_t>(4);
+        visit = ar.take<uint32_t>(n);
+        left = ar.take<int>(n); right = ar.take<int>(n); parent_internal = ar.take<int>(n); parent_leaf = ar.take<int>(n);
+        scan_local = ar.take<unsigned long long>(n); scan_sums = ar.take<unsigned long long>((size_t)max_sblk + 1);
+        area_sum = ar.take<float>(4);
+        S = carve_sah(ar, choice == RT_BUILD_PLOC ? std::min<uint32_t>(n, ploc_top + 64u) : n);
+    };
+    { Arena measure(nullptr); carve(measure); RT_CUDA(ds.scratch.reserve(measure.off + 256)); }
+    { Arena ar(ds.scratch.p); carve(ar); }
+    RT_CUDA(ds.readback.reserve(sizeof(SahCtl) + 512));
+    SahCtl* h_ctl = (SahCtl*)ds.readback.p;
+    char* h_misc = (char*)ds.readback.p + ((sizeof(SahCtl) + 63) & ~size_t(63));
+    unsigned long long* h_tot = (unsigned long long*)h_misc;              // PLOC round totals
+    uint32_t* h_ord = (uint32_t*)(h_misc + 64);                           // initial centroid bounds
+    float4* h_root = (float4*)(h_misc + 128);
+    float* h_area = (float*)(h_misc + 192);
+
+    const uint32_t ord_init[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
+    memcpy(h_ord, ord_init, sizeof(ord_init));
+    RT_CUDA(cudaMemcpyAsync(scene_ord, h_ord, sizeof(ord_init), cudaMemcpyHostToDevice, stream));
+
+    RT_CUDA(cudaEventRecord(ev[0], stream));
+    k_prim_bounds<<<gb, tb, 0, stream>>>(ds.view, d_prims_in, n, time_lo, time_hi, box_lo, box_hi, scene_ord);
+    k_morton<<<gb, tb, 0, stream>>>(box_lo, box_hi, n, scene_ord, keys_a, vals_a);
+    RT_CUDA(cudaEventRecord(ev[1], stream));
+    uint64_t *kin = keys_a, *kout = keys_b;
+    uint32_t *vin = vals_a, *vout = vals_b;
+    for (int pass = 0; pass < 8; pass++) {   // 63-bit codes: 8 passes of 8 bits
+        const int shift = 8 * pass;
+        k_sort_hist<<<nblocks, SORT_THREADS, 0, stream>>>(kin, n, shift, counts);
+        k_sort_scan<<<1, 1024, 0, stream>>>(counts, 256 * nblocks, nblocks, n, trivial);
+        k_sort_scatter<<<nblocks, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, counts, trivial);
+        std::swap(kin, kout); std::swap(vin, vout);
+    }
+    RT_CUDA(cudaEventRecord(ev[2], stream));
+    ds.build.build_rounds = 0; ds.build.ploc_radius = 0; ds.build.bvh_depth = 0; ds.build.sah_internal = 0.f;
+
+    bool built = false;
+    if (choice == RT_BUILD_GPU_SAH) {
+        // leaves in Morton order (the order the primitives are stored in): leaf i = sorted position i
+        k_ploc_init<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, leaf_lo, leaf_hi);
+        uint32_t levels = 0;
+        const int rc = sah_sweep_gpu(S, leaf_lo, leaf_hi, nullptr, false, n, nodes, sms, stream, &levels);
+        if (rc < 0) return rc;
+        RT_CUDA(cudaMemcpyAsync(h_ctl, S.ctl, sizeof(SahCtl), cudaMemcpyDeviceToHost, stream));
+        RT_CUDA(cudaEventRecord(ev[3], stream));
+        RT_CUDA(cudaEventRecord(ev[4], stream));
+        ds.pending.sah_levels = levels;   // checked by build_bvh_finish after the commit's synchronisation
+        ds.build.builder = RT_BUILDER_GPU_SAH;
+        built = true;
+    } else if (choice == RT_BUILD_HOST_SAH) {
+        std::vector<float4> h_lo(n), h_hi(n);
+        std::vector<uint32_t> h_ordv(n);
+        RT_CUDA(cudaMemcpyAsync(h_lo.data(), box_lo, sizeof(float4) * n, cudaMemcpyDeviceToHost, stream));
+        RT_CUDA(cudaMemcpyAsync(h_hi.data(), box_hi, sizeof(float4) * n, cudaMemcpyDeviceToHost, stream));
+        RT_CUDA(cudaMemcpyAsync(h_ordv.data(), vin, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, stream));
+        RT_CUDA(cudaStreamSynchronize(stream));
+        std::vector<HostBox> leaf(n);
+        for (uint32_t i = 0; i < n; i++) {
+            const float4 l = h_lo[h_ordv[i]], h = h_hi[h_ordv[i]];
+            leaf[i] = HostBox{{l.x, l.y, l.z}, {h.x, h.y, h.z}};
+        }
+        SahBuilder b(leaf);
+        const SahBuilder::Result root = b.build(0, n, 0, 0);
+        if (root.depth + 2 <= RT_STACK_DEPTH) {
+            RT_CUDA(cudaMemcpyAsync(nodes, b.nodes.data(), sizeof(BNode) * n_nodes, cudaMemcpyHostToDevice, stream));
+            RT_CUDA(cudaStreamSynchronize(stream));
+            RT_CUDA(cudaEventRecord(ev[3], stream));
+            RT_CUDA(cudaEventRecord(ev[4], stream));
+            ds.build.bvh_depth = root.depth;
+            ds.build.sah_internal = (float)(root.area_sum / std::max(half_area(root.box), 1e-30f));
+            ds.build.builder = RT_BUILDER_HOST_SAH;
+            built = true;
+        } else choice = RT_BUILD_PLOC;
+    }
+    if (built) {
+        // nodes are in place (GPU sweep: queued)
+    } else if (choice == RT_BUILD_KARRAS) {
+        ds.build.builder = RT_BUILDER_KARRAS;
+        RT_CUDA(cudaMemsetAsync(visit, 0, sizeof(uint32_t) * n, stream));
+        if (n > 1) k_karras<<<gb, tb, 0, stream>>>(kin, (int)n, left, right, parent_internal, parent_leaf);
+        RT_CUDA(cudaEventRecord(ev[3], stream));
+        k_refit<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, right, parent_internal, parent_leaf, leaf_lo, leaf_hi, node_lo, node_hi, visit);
+        RT_CUDA(cudaEventRecord(ev[4], stream));
+        k_emit_nodes<<<gb, tb, 0, stream>>>((int)n, left, right, leaf_lo, leaf_hi, node_lo, node_hi, nodes);
+    } else {
+        // PLOC: cluster lists ping-pong between (cid_a, leaf_*) and (cid_b, node_*); `left`/`right` double as cid arrays,
+        // `parent_internal` as the nearest-neighbour array.  The search radius trades differently per scene (flat rect
+        // soups like a wide window less than triangle meshes do), and a build is ~1 ms per 250 k primitives, so scenes up
+        // to PLOC_SWEEP_MAX primitives are built with several radii and the tree with the smallest summed internal-node
+        // area (the SAH traversal term) is kept; measured node visits per ray follow that sum (profiles/r01_v5_ploc.md).
+        RT_CUDA(cudaEventRecord(ev[3], stream));
+        std::vector<int> radii;
+        if (bs.ploc_radius) radii.push_back(std::min<int>(PLOC_MAX_RADIUS, std::max<int>(1, (int)bs.ploc_radius)));
+        else if (n <= PLOC_SWEEP_MAX) radii = {4, 8, 16, 32};
+        else radii = {16};
+        BNode* nodes_alt = nullptr;
+        if (radii.size() > 1) { RT_CUDA(ds.nodes_alt.reserve(sizeof(BNode) * (size_t)n_nodes)); nodes_alt = (BNode*)ds.nodes_alt.p; }
+        const int total_internal = (int)n - 1;
+        float best_area = INFINITY;
+        BNode* best_nodes = nullptr;
+        for (const int radius : radii) {
+            BNode* target = best_nodes == nodes ? nodes_alt : nodes;          // never overwrite the best tree so far
+            int *cid_in = left, *cid_out = right, *nn = parent_internal;
+            float4 *lo_in = leaf_lo, *hi_in = leaf_hi, *lo_out = node_lo, *hi_out = node_hi;
+            RT_CUDA(cudaMemsetAsync(area_sum, 0, sizeof(float), stream));
+            k_ploc_init<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, cid_in, lo_in, hi_in);
+            int cur_n = (int)n, created = 0, rounds = 0;
+            // Hybrid: agglomeration stops once at most `top_n` clusters are left and the TOP of the tree — the levels every
+            // ray walks, and where bounded-radius clustering is weakest — is built over the cluster boxes by the SAH sweep
+            // (on the GPU since round 2).  PLOC numbers its nodes from the high indices down, so the top gets [0, clusters - 1).
+            // 1 M triangles: 26.7 -> 24.4 node visits per ray, extend -8 % (top of 32 k clusters; 25.0 with 2 k).
+            // Scenes below 16 k primitives — PLOC only when asked for — stay pure PLOC for A/B.
+            const int top_n = n >= 16384u ? std::min<int>((int)ploc_top, (int)(n / 8u)) : 1;
+            while (cur_n > top_n) {
+                const int nblk = (cur_n + PLOC_BLOCK - 1) / PLOC_BLOCK, sblk = (cur_n + SCAN_TILE - 1) / SCAN_TILE;
+                k_ploc_nn<<<nblk, PLOC_BLOCK, 0, stream>>>(lo_in, hi_in, cur_n, nn, radius);
+                k_ploc_scan_block<<<sblk, PLOC_BLOCK, 0, stream>>>(nn, cur_n, scan_local, scan_sums);
+                k_ploc_scan_sums<<<1, 1024, 0, stream>>>(scan_sums, sblk);
+                k_ploc_merge<<<nblk, PLOC_BLOCK, 0, stream>>>(nn, cur_n, scan_local, scan_sums, cid_in, lo_in, hi_in, cid_out, lo_out, hi_out, target,
+                                                              total_internal - 1 - created, area_sum);
+                RT_CUDA(cudaMemcpyAsync(h_tot, scan_sums + sblk, sizeof(*h_tot), cudaMemcpyDeviceToHost, stream));
+                RT_CUDA(cudaStreamSynchronize(stream));
+                const unsigned long long tot = *h_tot;
+                const int survivors = (int)(uint32_t)tot, merges = (int)(tot >> 32);
+                if (merges <= 0 || survivors != cur_n - merges) { set_error("bvh build: PLOC round made no progress (internal error)"); return RT_ERR_STATE; }
+                cur_n = survivors; created += merges; rounds++;
+                std::swap(cid_in, cid_out); std::swap(lo_in, lo_out); std::swap(hi_in, hi_out);
+            }
+            if (created + cur_n - 1 != total_internal) { set_error("bvh build: PLOC node count mismatch (internal error)"); return RT_ERR_STATE; }
+            float root_lo[3], root_hi[3];
+            float area = 0.f;
+            uint32_t depth = 0;
+            if (cur_n > 1) {   // top of the tree over the remaining clusters: SAH sweep, leaf codes = cluster ids, depths in lo.w
+                uint32_t levels = 0;
+                const int rc = sah_sweep_gpu(S, lo_in, hi_in, cid_in, true, (uint32_t)cur_n, target, sms, stream, &levels);
+                if (rc < 0) return rc;
+                RT_CUDA(cudaMemcpyAsync(h_ctl, S.ctl, sizeof(SahCtl), cudaMemcpyDeviceToHost, stream));
+                RT_CUDA(cudaMemcpyAsync(h_area, area_sum, sizeof(float), cudaMemcpyDeviceToHost, stream));
+                RT_CUDA(cudaStreamSynchronize(stream));
+                if (h_ctl->too_deep || h_ctl->nseg[levels] != 0) continue;
+                memcpy(root_lo, h_ctl->root_lo, 12); memcpy(root_hi, h_ctl->root_hi, 12);
+                area = *h_area + (float)h_ctl->area_sum;
+                depth = h_ctl->depth;
+            } else {
+                RT_CUDA(cudaMemcpyAsync(h_root, lo_in, sizeof(float4), cudaMemcpyDeviceToHost, stream));
+                RT_CUDA(cudaMemcpyAsync(h_root + 1, hi_in, sizeof(float4), cudaMemcpyDeviceToHost, stream));
+                RT_CUDA(cudaMemcpyAsync(h_area, area_sum, sizeof(float), cudaMemcpyDeviceToHost, stream));
+                RT_CUDA(cudaStreamSynchronize(stream));
+                root_lo[0] = h_root[0].x; root_lo[1] = h_root[0].y; root_lo[2] = h_root[0].z;
+                root_hi[0] = h_root[1].x; root_hi[1] = h_root[1].y; root_hi[2] = h_root[1].z;
+                area = *h_area;
+                depth = (uint32_t)h_root[0].w;
+            }
+            if (depth + 2 > RT_STACK_DEPTH) continue;                         // deeper than the traversal supports: not a candidate
+            if (area < best_area) {
+                best_area = area; best_nodes = target;
+                const float rdx = root_hi[0] - root_lo[0], rdy = root_hi[1] - root_lo[1], rdz = root_hi[2] - root_lo[2];
+                ds.build.bvh_depth = depth;
+                ds.build.sah_internal = area / fmaxf(rdx * rdy + rdy * rdz + rdz * rdx, 1e-30f);
+                ds.build.build_rounds = (uint32_t)rounds;
+                ds.build.ploc_radius = (uint32_t)radius;
+                ds.build.builder = RT_BUILDER_PLOC;
+            }
+        }
+        if (!best_nodes) { set_error("bvh build: tree deeper than the traversal supports; commit with rt_build_settings::builder = RT_BUILD_KARRAS"); return RT_ERR_UNSUPPORTED; }
+        if (best_nodes == nodes_alt) { std::swap(ds.nodes, ds.nodes_alt); nodes = (BNode*)ds.nodes.p; }
+        RT_CUDA(cudaEventRecord(ev[4], stream));
+    }
+    k_permute_prims<<<gb, tb, 0, stream>>>(n, vin, d_prims_in, d_leaf_ids_in, prims_out, leaf_ids_out);
+    RT_CUDA(cudaEventRecord(ev[5], stream));
+    RT_CUDA(cudaGetLastError());
+
+    ds.view.prims = prims_out; ds.view.prim_leaf_id = leaf_ids_out; ds.view.nodes = nodes;
+    ds.view.n_nodes = n_nodes;
+    ds.build.n_nodes = n_nodes;
+    return RT_OK;
+}
+
+int build_bvh_finish(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t stream) {
+    if (!ds.pending.sah_levels) return RT_OK;
+    const SahCtl* h_ctl = (const SahCtl*)ds.readback.p;
+    const uint32_t levels = ds.pending.sah_levels;
+    ds.pending.sah_levels = 0;
+    if (h_ctl->too_deep || h_ctl->nseg[levels] != 0) {
+        // deeper than the launches queued (or than the traversal supports): thousands of identical boxes.  PLOC's balanced
+        // merges take over — a second build, paid only by such scenes.
+        rt_build_settings again = bs;
+        again.builder = RT_BUILD_PLOC;
+        const int rc = build_bvh(ds, again, ds.pending.prims_in, ds.pending.leaf_in, ds.pending.n, ds.pending.t_lo, ds.pending.t_hi, stream);
+        if (rc < 0) return rc;
+        RT_CUDA(cudaStreamSynchronize(stream));
+        return RT_OK;
+    }
+    ds.build.bvh_depth = h_ctl->depth;
+    const float rx = h_ctl->root_hi[0] - h_ctl->root_lo[0], ry = h_ctl->root_hi[1] - h_ctl->root_lo[1], rz = h_ctl->root_hi[2] - h_ctl->root_lo[2];
+    ds.build.sah_internal = (float)(h_ctl->area_sum / std::max(rx * ry + ry * rz + rz * rx, 1e-30f));
+    ds.build.build_rounds = h_ctl->depth;
+    return RT_OK;
+}
+
+} // namespace rtb
