@@ -10,11 +10,14 @@
 //   extend           persistent warps claim 32 consecutive paths, traverse the BVH + media (render.h:63) and
 //                    write an 8-byte hit record + a 1-byte material class at the same position.  Leaf tests are
 //                    parked and run warp-wide (traverse.cuh).
-//   shade            persistent blocks claim tiles of 256 consecutive paths, sort the tile by material class in
-//                    shared memory (so a warp shades one class), evaluate hit attributes / textures / scatter,
+//   shade            persistent WARPS claim tiles of 256 consecutive paths, rank them by material class with ballots
+//                    (8 rounds of 32 paths, a round shades one class), evaluate hit attributes / textures / scatter,
 //                    add thr*L of terminated paths to the accumulation buffer (float atomics), REGENERATE
 //                    terminated paths from the global sample cursor, and append survivors / new camera paths to
-//                    pool `next`.  All allocation is block-aggregated: three atomics per 256 paths.
+//                    pool `next`.  Whether a path continues is known from its class byte alone (extend adds a
+//                    last-bounce bit), so a warp allocates for its tile BEFORE it shades — three atomics per 256
+//                    paths whose latency hides behind the ranking — and no barrier, block-wide sort or
+//                    single-thread allocator is left (round 1: 37 % of k_shade's stall samples were barriers).
 //   turnover         one thread: roll the counters and publish the live-path count to pinned host memory.
 // The pools stay full until the samples run out; the host never synchronises inside a frame (it polls the
 // live count a few iterations behind).
@@ -23,7 +26,6 @@
 #include "shade.cuh"
 #include "traverse.cuh"
 
-#include <cuda_pipeline.h>
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -32,11 +34,15 @@
 
 namespace rtb {
 
-constexpr int NQ = 6;                 // material classes: 0 = miss, 1 + rt_material_type
-constexpr int Q_MISS = 0;
+// class byte written by extend: bits 0-2 = class, bit 3 = last bounce (the path cannot continue whatever it hits)
+constexpr int Q_MISS = 0;             // 1 + rt_material_type = 1 .. 5
+constexpr int Q_LIGHT = 1 + RT_MAT_DIFFUSE_LIGHT;
+constexpr int Q_DEAD = 6;             // a slot reserved for a path that was then absorbed (metal scattering into the surface): ends here, regenerates
+constexpr int Q_HOLE = 7;             // no path: the tile tail and (deferred extend) the slot of a suspended path
+constexpr int Q_LAST = 8;
+constexpr uint32_t DEAD_BOUNCE = 0xffu;   // bounce byte of a dead slot's ray word (live rays: bounce + 1 < max_depth <= 254)
 constexpr int POLL_DEPTH = 4;         // host runs this many iterations ahead of the counter it polls
 constexpr int POLL_SLOTS = 8;
-constexpr int Q_SUSP = NQ;            // deferred extend: the walk of this path is suspended and the path has moved into its continuation record
 
 // every hot counter on its own 128-byte line (its own L2 slice): same-line atomics serialise
 struct __align__(128) Counters {
@@ -50,6 +56,7 @@ struct __align__(128) Counters {
     unsigned long long pad5[11];
     struct { uint32_t n, pad[31]; } cont[2];      // continuation records in list b (written by the extend of iterations with cur = b)
     struct { uint32_t n, pad[31]; } n_fin[2];     // resumed paths that finished their walk in this iteration: region [capacity, capacity + n) of pool b
+    struct { uint32_t n, pad[31]; } n_dead[2];    // dead slots shade wrote into pool b (not path segments: subtracted from total_rays)
 };
 
 struct PoolView {
@@ -59,7 +66,7 @@ struct PoolView {
     uint2* hit;          // written by extend: bits of t, Closest::prim
     uint8_t* hit_class;  // written by extend: material class of the hit
     // continuation records of suspended walks (k_extend_defer), two lists: extend(cur) reads list cur ^ 1 and writes list cur.
-    // A record owns its path: the pool slot it came from is a hole (class Q_SUSP) that shade skips.
+    // A record owns its path: the pool slot it came from is a hole (class Q_HOLE) that shade skips.
     uint4* cont_walk[2];   // bits of the closest t so far, its primitive, node, parked leaf
     float4* cont_o[2];     // the path: ray origin + time,
     float4* cont_d[2];     //   direction + sample / bounce word,
@@ -77,24 +84,18 @@ struct RenderPool {
     Counters* h_counters = nullptr;   // pinned copy for stats
     cudaEvent_t poll_ev[POLL_SLOTS]{};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    int grid_extend = 0, grid_shade = 0, shade_block = 256;
+    int grid_extend = 0, grid_shade = 0, grid_shade_block = 0;
+    int extend_variant = -1;               // traversal variant the extend grid was sized for
     cudaGraphExec_t graph_exec = nullptr;   // GRAPH_ITERS wavefront iterations as one CUDA graph (render_impl)
     cudaStream_t capture_stream = nullptr;
-    RenderPool* second = nullptr;        // two-lane rendering: the second lane's pools (owned)
-    cudaStream_t own_stream = nullptr;   //   and its stream
-    cudaEvent_t ev_extend = nullptr;     //   recorded after each extend launch of this lane
-    int lanes = 1;
     uint32_t suspend_below = 0;          // deferred extend (k_extend_defer): a full warp suspends once <= this many lanes are live; 0 = k_extend
     std::vector<cudaEvent_t> timer_ev;   // RT_RENDER_TIMERS: 3 events per iteration, reused across frames
 };
 
 void render_pool_destroy(RenderPool* p) {
     if (!p) return;
-    render_pool_destroy(p->second);
     if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
     if (p->capture_stream) cudaStreamDestroy(p->capture_stream);
-    if (p->own_stream) cudaStreamDestroy(p->own_stream);
-    if (p->ev_extend) cudaEventDestroy(p->ev_extend);
     for (int b = 0; b < 2; b++) { cudaFree(p->v.ray_o[b]); cudaFree(p->v.ray_d[b]); cudaFree(p->v.thr[b]); }
     cudaFree(p->v.hit); cudaFree(p->v.hit_class); cudaFree(p->v.c);
     for (int b = 0; b < 2; b++) {
@@ -115,7 +116,7 @@ namespace {
 struct FrameParams {
     uint32_t width, height, max_depth, seed;
     uint32_t sample_first;
-    uint32_t pad;
+    uint32_t debug;                     // rt_debug_flags
     unsigned long long total_samples;   // samples this call renders = npix * sample_count
     unsigned long long npix, npix_magic; // film indices this call covers (the frame, or this tile-split share) and ceil(2^64 / npix)
     float* accum;                       // width*height*3 sums
@@ -133,10 +134,10 @@ __device__ __forceinline__ uint32_t pos_of(uint32_t idx, uint32_t n_bounce, uint
     return idx < n_bounce ? idx : capacity - n + idx;
 }
 
-// persistent work fetch: a warp claims 32 consecutive paths
-__device__ __forceinline__ uint32_t warp_claim(uint32_t* cursor) {
+// persistent work fetch: a warp claims `n` consecutive paths
+__device__ __forceinline__ uint32_t warp_claim(uint32_t* cursor, uint32_t n = 32u) {
     uint32_t base = 0;
-    if ((threadIdx.x & 31) == 0) base = atomicAdd(cursor, 32u);
+    if ((threadIdx.x & 31) == 0) base = atomicAdd(cursor, n);
     return __shfl_sync(0xffffffffu, base, 0);
 }
 
@@ -182,7 +183,7 @@ __device__ __forceinline__ void start_path(const SceneView& sv, const PoolView& 
         const uint32_t k = index / RT_TILE_BLOCK_PIXELS;
         index = (k * fp.tile_count + fp.tile_index) * RT_TILE_BLOCK_PIXELS + (index - k * RT_TILE_BLOCK_PIXELS);
     }
-    if (fp.pad & 1u) { py = index / fp.width; px = index - py * fp.width; } else film_xy(fp, index, px, py);
+    if (fp.debug & RT_DEBUG_RASTER_FILM) { py = index / fp.width; px = index - py * fp.width; } else film_xy(fp, index, px, py);
     const uint32_t pixel = py * fp.width + px;
     const RngKey key{pixel, sample, 0u, fp.seed};
     const Ray r = camera_ray(sv.camera, key, (int)px, (int)py, (int)fp.width, (int)fp.height);
@@ -198,9 +199,24 @@ __global__ void __launch_bounds__(256) k_generate(SceneView sv, PoolView pv, Fra
     if (i < n_fresh) start_path(sv, pv, fp, 0, pv.capacity - n_fresh + i, i);
 }
 
+// class byte of a finished walk
+__device__ __forceinline__ uint8_t hit_class_of(const SceneView& sv, const Closest& c, uint32_t bounce, uint32_t max_depth) {
+    int q = Q_MISS;
+    if (c.prim != -1) {
+        const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
+        q = 1 + (int)sv.materials[mat].type;
+    }
+    if (bounce + 1 >= max_depth) q |= Q_LAST;                   // render.h:60: the next segment would start at depth 0
+    return (uint8_t)q;
+}
+
 // ---- extend ---------------------------------------------------------------------------------------
-template <bool COUNT, bool PARKED = false>
+// V: traversal variant (traverse.cuh: TV_TCULL | TV_SMEM | TV_MINMAX)
+template <bool COUNT, int V>
 __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+    constexpr bool SM = (V & TV_SMEM) != 0, TC = (V & TV_TCULL) != 0;
+    __shared__ int s_stack[SM ? RT_SHORT_STACK * (TC ? 2 : 1) * EXTEND_BLOCK : 1];
+    int* column = s_stack + (SM ? threadIdx.x : 0);
     const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
     const uint32_t lane = threadIdx.x & 31;
     const float4* __restrict__ ray_o = pv.ray_o[cur];
@@ -212,27 +228,23 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
         const uint32_t base = warp_claim(&pv.c->cur_extend);
         if (base >= n) break;
         const uint32_t idx = base + lane;
-        const bool active = idx < n;                // closest_hit is warp-collective
+        const bool in_range = idx < n;              // closest_hit is warp-collective
         const uint32_t nodes_before = tc.nodes;
-        const uint32_t pos = pos_of(active ? idx : base, n_b, n, pv.capacity);
+        const uint32_t pos = pos_of(in_range ? idx : base, n_b, n, pv.capacity);
         const float4 o = ray_o[pos], d = ray_d[pos];
+        const uint32_t sb = __float_as_uint(d.w);
+        const bool dead = (sb >> 24) == DEAD_BOUNCE;
         Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
         // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched
         // when a ray really crosses a medium boundary
-        const Closest c = closest_hit<COUNT, PARKED>(sv, r, 0.001f, true, [&](uint32_t m) {                      // render.h:63
-            const uint32_t sb = __float_as_uint(d.w);
+        const Closest c = closest_hit<COUNT, V, EXTEND_BLOCK>(sv, r, 0.001f, true, [&](uint32_t m) {                // render.h:63
             const RngKey key{__float_as_uint(thr[pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
             return draw4(key, RT_STREAM_MEDIUM, m).x;
-        }, &tc, active);
+        }, &tc, in_range && !dead, column);
         if (COUNT) slots += 32ull * __reduce_max_sync(0xffffffffu, tc.nodes - nodes_before);   // node steps the warp paid for
-        if (active) {
-            int q = Q_MISS;
-            if (c.prim != -1) {
-                const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
-                q = 1 + (int)sv.materials[mat].type;
-            }
+        if (in_range) {
             pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
-            pv.hit_class[pos] = (uint8_t)q;
+            pv.hit_class[pos] = dead ? (uint8_t)Q_DEAD : hit_class_of(sv, c, sb >> 24, fp.max_depth);
         }
     }
     if (COUNT) {
@@ -244,7 +256,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
 
 // Deferred extend (walk_suspendable): a warp stops walking once no more than `suspend_below` of its 32 rays are still
 // live and moves those paths — ray, throughput, traversal state — into a continuation list; their pool slots become holes
-// (class Q_SUSP) that shade skips.  The NEXT iteration's extend takes the suspended walks up again, 32 stragglers to a
+// (class Q_HOLE) that shade skips.  The NEXT iteration's extend takes the suspended walks up again, 32 stragglers to a
 // warp, before it starts on the pool (longest work first); a resumed path that finishes its walk is written, with its hit
 // record, to the region [capacity, capacity + n_fin) of the current pool, which shade treats like any other path.  A
 // suspended path simply bounces an iteration later.  Nothing waits for stragglers: a second pass inside the same
@@ -272,6 +284,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
         Walk w{RT_NODE_DONE, RT_NODE_DONE, 0};
         Closest c; c.t = INFINITY; c.prim = -1;
         uint32_t pos = 0;
+        bool dead = false;
         float4 o, d, th = make_float4(0.f, 0.f, 0.f, 0.f);
         if (resumed) {
             const uint32_t rec = active ? idx : base;
@@ -286,7 +299,8 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
         } else {
             pos = pos_of(active ? idx : idx - lane, n_b, n_pool, pv.capacity);
             o = pv.ray_o[cur][pos]; d = pv.ray_d[cur][pos];
-            if (active && sv.n_prims) w.node = 0;
+            dead = (__float_as_uint(d.w) >> 24) == DEAD_BOUNCE;
+            if (active && !dead && sv.n_prims) w.node = 0;
         }
         Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
         // only whole batches suspend: a few stragglers left over at the end of a list would otherwise advance a leaf phase per iteration
@@ -299,7 +313,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
             if (lane == (uint32_t)(__ffs(ms) - 1)) slot = atomicAdd(&pv.c->cont[wr].n, (uint32_t)__popc(ms));
             slot = __shfl_sync(0xffffffffu, slot, __ffs(ms) - 1) + __popc(ms & lt);
             if (suspended) {
-                if (!resumed) { th = pv.thr[cur][pos]; pv.hit_class[pos] = (uint8_t)Q_SUSP; }
+                if (!resumed) { th = pv.thr[cur][pos]; pv.hit_class[pos] = (uint8_t)Q_HOLE; }
                 pv.cont_o[wr][slot] = o; pv.cont_d[wr][slot] = d; pv.cont_thr[wr][slot] = th;
                 pv.cont_walk[wr][slot] = make_uint4(__float_as_uint(c.t), (uint32_t)c.prim, (uint32_t)w.node, (uint32_t)w.parked);
                 pv.cont_sp[wr][slot] = (uint8_t)w.sp;
@@ -318,129 +332,20 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
             }
         }
         if (finished) {
+            const uint32_t sb = __float_as_uint(d.w);
             // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched when a ray really crosses a boundary
-            if (sv.n_active_media) closest_medium(sv, r, 0.001f, c, [&](uint32_t m) {
-                const uint32_t sb = __float_as_uint(d.w);
+            if (sv.n_active_media && !dead) closest_medium(sv, r, 0.001f, c, [&](uint32_t m) {
                 const RngKey key{__float_as_uint(resumed ? th.w : pv.thr[cur][pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
                 return draw4(key, RT_STREAM_MEDIUM, m).x;
             });
-            int q = Q_MISS;
-            if (c.prim != -1) {
-                const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
-                q = 1 + (int)sv.materials[mat].type;
-            }
             pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
-            pv.hit_class[pos] = (uint8_t)q;
+            pv.hit_class[pos] = dead ? (uint8_t)Q_DEAD : hit_class_of(sv, c, sb >> 24, fp.max_depth);
         }
     }
     if (COUNT) {
         atomicAdd(&pv.c->nodes, (unsigned long long)tc.nodes);
         atomicAdd(&pv.c->prim_tests, (unsigned long long)tc.prim_tests);
         if (lane == 0) atomicAdd(&pv.c->node_slots, 32ull * steps);
-    }
-}
-
-// Streaming variant (closest_surface_stream): finished lanes are refilled from the queue while the rest of the warp
-// keeps walking.  Same results ray by ray; only which lane traces which ray changes.
-// A refill must not cost a round trip to the queue cursor plus one to the pool (both DRAM latencies, paid with most of
-// the warp waiting): every warp keeps a ring of 64 staged rays in shared memory, filled 32 at a time by cp.async from
-// a chunk whose queue position was claimed one refill earlier, so the atomic and the loads are in flight while the
-// warp traverses and a refill reads shared memory only.
-#ifndef RT_REFILL_BELOW
-#define RT_REFILL_BELOW 24
-#endif
-constexpr uint32_t RING = 64, RING_INVALID = 0xffffffffu;
-struct StreamShared {
-    float4 ring_o[EXTEND_BLOCK / 32][RING], ring_d[EXTEND_BLOCK / 32][RING];   // staged rays, per warp
-    float4 lane_o[EXTEND_BLOCK], lane_d[EXTEND_BLOCK];                          // the ray each lane traces (LaneSlots)
-    float4 obj_o[EXTEND_BLOCK], obj_d[EXTEND_BLOCK];
-    float4 inv_d[EXTEND_BLOCK], inv_o[EXTEND_BLOCK];
-    uint32_t ring_pos[EXTEND_BLOCK / 32][RING];
-    uint32_t lane_pos[EXTEND_BLOCK];                                            // its pool slot
-    uint32_t q[EXTEND_BLOCK / 32][4];                                           // per warp: handed out, staged, -, staged all
-};
-template <bool COUNT>
-__global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend_stream(SceneView sv, PoolView pv, FrameParams fp, int cur) {
-    __shared__ StreamShared sh;
-    const uint32_t n_b = pv.c->n_bounce[cur], n = n_b + pv.c->n_fresh[cur];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    TraversalCounters tc{0, 0};
-    unsigned long long slots = 0;
-    uint32_t next_base = 0;              // lane 0: queue position of the next chunk to stage, claimed one refill ahead
-    if (lane == 0) {                     // (a register, so that nobody waits for the atomic before the value is needed)
-        sh.q[warp][0] = 0; sh.q[warp][1] = 0; sh.q[warp][3] = 0;
-        next_base = atomicAdd(&pv.c->cur_extend, 32u);
-    }
-    __syncwarp();
-    const LaneSlots ls{&sh.lane_o[threadIdx.x], &sh.lane_d[threadIdx.x], &sh.obj_o[threadIdx.x], &sh.obj_d[threadIdx.x],
-                       &sh.inv_d[threadIdx.x], &sh.inv_o[threadIdx.x]};
-    closest_surface_stream<COUNT, RT_REFILL_BELOW>(sv, 0.001f, ls,                                              // render.h:63
-        [&](bool fin, uint32_t fm, bool& valid, Closest& c) {
-            const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
-            float4* ring_o = sh.ring_o[warp];
-            float4* ring_d = sh.ring_d[warp];
-            uint32_t* ring_pos = sh.ring_pos[warp];
-            volatile uint32_t* q = sh.q[warp];
-            if (fin && valid) {
-                const uint32_t pos = sh.lane_pos[threadIdx.x];
-                if (sv.n_active_media) {
-                    const Ray r = lane_ray(ls);
-                    const uint32_t sb = __float_as_uint(lds4(ls.ray_d).w);
-                    closest_medium(sv, r, 0.001f, c, [&](uint32_t m) {   // free-flight draw keyed (pixel, sample, bounce, m)
-                        const RngKey key{__float_as_uint(pv.thr[cur][pos].w), sb & 0xffffffu, sb >> 24, fp.seed};
-                        return draw4(key, RT_STREAM_MEDIUM, m).x;
-                    });
-                }
-                int qc = Q_MISS;
-                if (c.prim != -1) {
-                    const uint32_t mat = c.prim >= 0 ? sv.prims[c.prim].material : sv.media[-2 - c.prim].material;
-                    qc = 1 + (int)sv.materials[mat].type;
-                }
-                pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
-                pv.hit_class[pos] = (uint8_t)qc;
-                valid = false;
-            }
-            // hand out staged rays
-            __pipeline_wait_prior(0);
-            __syncwarp();
-            uint32_t head = q[0], tail = q[1];
-            const uint32_t avail = tail - head, want = (uint32_t)__popc(fm), rank = (uint32_t)__popc(fm & lt);
-            if (fin && rank < avail) {
-                const uint32_t slot = (head + rank) & (RING - 1);
-                const uint32_t p = ring_pos[slot];
-                if (p != RING_INVALID) {
-                    sts4(ls.ray_o, lds4(&ring_o[slot]));
-                    sts4(ls.ray_d, lds4(&ring_d[slot]));
-                    sh.lane_pos[threadIdx.x] = p;
-                    valid = true;
-                }
-            }
-            head += min(want, avail);
-            __syncwarp();
-            // stage the chunk claimed earlier, claim the one after it
-            bool staged_all = q[3] != 0;
-            while (!staged_all && tail - head <= RING - 32) {
-                const uint32_t base = __shfl_sync(0xffffffffu, next_base, 0);
-                if (base >= n) { staged_all = true; break; }
-                const uint32_t idx = base + lane, slot = (tail + lane) & (RING - 1);
-                if (idx < n) {
-                    const uint32_t p = pos_of(idx, n_b, n, pv.capacity);
-                    ring_pos[slot] = p;
-                    __pipeline_memcpy_async(&ring_o[slot], &pv.ray_o[cur][p], 16);
-                    __pipeline_memcpy_async(&ring_d[slot], &pv.ray_d[cur][p], 16);
-                } else ring_pos[slot] = RING_INVALID;
-                __pipeline_commit();
-                tail += 32;
-                if (lane == 0) next_base = atomicAdd(&pv.c->cur_extend, 32u);
-            }
-            if (lane == 0) { q[0] = head; q[1] = tail; q[3] = staged_all ? 1u : 0u; }
-            __syncwarp();
-            return staged_all && head == tail;
-        }, &tc, &slots);
-    if (COUNT) {
-        atomicAdd(&pv.c->nodes, (unsigned long long)tc.nodes);
-        atomicAdd(&pv.c->prim_tests, (unsigned long long)tc.prim_tests);
-        if (lane == 0) atomicAdd(&pv.c->node_slots, slots);
     }
 }
 
@@ -451,20 +356,59 @@ __device__ __forceinline__ void accumulate(float* accum, uint32_t pixel, float3 
     if (c.z != 0.f) atomicAdd(&accum[3 * (size_t)pixel + 2], c.z);
 }
 
-template <int SHADE_BLOCK, bool DEFER>
-__device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
-    constexpr int SHADE_WARPS = SHADE_BLOCK / 32;
-    constexpr int NP = NQ;                           // "no path": the tile tail and (deferred extend) the holes suspended paths leave
-    constexpr int NC = NP + 1;
-    __shared__ uint32_t s_tile[2];                   // this tile / the next one (claimed while this one is shaded)
-    constexpr int CELLS = NC * SHADE_WARPS <= 64 ? 2 : 4;   // class-table cells per lane of the scanning warp
-    __shared__ uint32_t s_cnt[32 * CELLS];           // [class][warp] counts -> exclusive offsets
-    __shared__ uint16_t s_perm[SHADE_BLOCK];         // sorted rank -> tile-local index | class << 12
-    __shared__ uint32_t s_wcont[SHADE_WARPS], s_wterm[SHADE_WARPS];
-    __shared__ uint32_t s_base_b, s_base_f, s_nregen;
-    __shared__ unsigned long long s_g0;
-    static_assert(NC * SHADE_WARPS <= 32 * CELLS, "class table must fit one warp scan");
+// what the class byte says about the path's future
+__device__ __forceinline__ bool class_continues(uint32_t c) {   // lambertian, metal, dielectric, isotropic with bounces left
+    const uint32_t k = c & 7u;
+    return !(c & (uint32_t)Q_LAST) && k >= 1u && k <= 5u && k != (uint32_t)Q_LIGHT;
+}
+__device__ __forceinline__ bool class_terminates(uint32_t c) { return (c & 7u) != (uint32_t)Q_HOLE && !class_continues(c); }
 
+// One path: hit attributes, emission / scatter.  Returns true when the path goes on (`out` filled); paths that end here
+// add their radiance to the accumulation buffer.
+struct ShadeOut { float4 o, d, thr; };
+__device__ __forceinline__ bool shade_path(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur, uint32_t pos, uint32_t k, bool last,
+                                           ShadeOut& out) {
+    if (k == (uint32_t)Q_DEAD || (last && k != (uint32_t)Q_LIGHT && k != (uint32_t)Q_MISS)) return false;   // absorbed earlier / depth exhausted (render.h:60): black
+    const float4 th = pv.thr[cur][pos];
+    const uint32_t pixel = __float_as_uint(th.w);
+    float3 thr = make_float3(th.x, th.y, th.z);
+    if (k == (uint32_t)Q_MISS) {
+        accumulate(fp.accum, pixel, thr * f3(sv.background[0], sv.background[1], sv.background[2]));   // render.h:64
+        return false;
+    }
+    const float4 d = pv.ray_d[cur][pos];
+    const float4 o = pv.ray_o[cur][pos];
+    const uint2 h = pv.hit[pos];
+    const uint32_t sb = __float_as_uint(d.w), sample = sb & 0xffffffu, bounce = sb >> 24;
+    Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
+    const int prim = (int)h.y;
+    const float t = __uint_as_float(h.x);
+    HitAttr rec;
+    uint32_t mat;
+    if (prim >= 0) { const DPrim p = sv.prims[prim]; prim_attr(sv, p, r, t, rec); mat = p.material; }
+    else { const DMedium m = sv.media[-2 - prim]; medium_attr(sv, m, r, t, rec); mat = m.material; }
+    const rt_flat_material m = sv.materials[mat];
+    if (m.type == RT_MAT_DIFFUSE_LIGHT) {
+        accumulate(fp.accum, pixel, thr * texture_value(sv, m.texture, rec.u, rec.v, rec.p));           // render.h:68, :75
+        return false;
+    }
+    const RngKey key{pixel, sample, bounce, fp.seed};
+    float3 attenuation;
+    Ray scattered;
+    if (!material_scatter(sv, m, r, rec, key, attenuation, scattered)) return false;                    // render.h:70-73: absorbed, black
+    thr = thr * attenuation;
+    out.o = make_float4(scattered.o.x, scattered.o.y, scattered.o.z, scattered.tm);
+    out.d = make_float4(scattered.d.x, scattered.d.y, scattered.d.z, __uint_as_float(sample | ((bounce + 1) << 24)));
+    out.thr = make_float4(thr.x, thr.y, thr.z, th.w);
+    return true;
+}
+
+constexpr int SHADE_BLOCK = 256, SHADE_WARPS = SHADE_BLOCK / 32;
+constexpr int WTILE = 256, WROUNDS = WTILE / 32;       // paths per warp tile / rounds of 32
+
+template <bool DEFER>
+__device__ __forceinline__ void shade_warp_tiles(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
+    __shared__ uint32_t s_perm[SHADE_WARPS][WTILE];   // sorted rank -> tile-local index | class byte << 8 | rank among the continuing (or ending) paths << 12
     const int next = cur ^ 1;
     // tile index space: bounced paths, fresh camera paths, (deferred extend) the resumed paths that finished at positions >= capacity
     const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
@@ -472,481 +416,96 @@ __device__ __forceinline__ void shade_tiles(const SceneView& sv, const PoolView&
     const unsigned long long iter_begin = pv.c->iter_begin;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
+    uint32_t* perm = s_perm[warp];
     auto pos_at = [&](uint32_t idx) { return DEFER && idx >= n_pool ? pv.capacity + (idx - n_pool) : pos_of(idx, n_b, n_pool, pv.capacity); };
-    if (threadIdx.x < 32 * CELLS) s_cnt[threadIdx.x] = 0;
-    if (threadIdx.x == 0) s_tile[0] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
-    __syncthreads();
-    auto class_of = [&](uint32_t tile) {             // material class of this thread's path in `tile` (NQ past the end)
-        const uint32_t idx = tile + threadIdx.x;
-        return idx < n ? min((int)pv.hit_class[pos_at(idx)], NP) : (int)NP;      // Q_SUSP == NP
+    // mask of the lanes whose class has bit pattern `k`, from the three bit ballots
+    auto class_mask = [](uint32_t b0, uint32_t b1, uint32_t b2, uint32_t k) {
+        return ((k & 1u) ? b0 : ~b0) & ((k & 2u) ? b1 : ~b1) & ((k & 4u) ? b2 : ~b2);
     };
-    uint32_t tile = s_tile[0];
-    int cls = class_of(tile);
-    for (int it = 0;; it ^= 1) {
-        if (tile >= n) break;
 
-        // -- sort the tile by material class (counting sort: ballots -> [class][warp] table -> one warp scan)
-        uint32_t e = threadIdx.x | ((uint32_t)cls << 12);
-        if (!(fp.pad & 32u)) {   // RT_EXP=32: unsorted tiles (A/B of the sort: profiles/r01_v9_experiments.md)
-            uint32_t rank = 0;
-            #pragma unroll
-            for (int k = 0; k < NC; k++) {
-                const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
-                if (cls == k) rank = __popc(m & lt);
-                if ((int)lane == k) s_cnt[k * SHADE_WARPS + warp] = __popc(m);
-            }
-            __syncthreads();
-            if (warp == 0) {
-                uint32_t v[CELLS], sum = 0;
-                #pragma unroll
-                for (int c = 0; c < CELLS; c++) { v[c] = s_cnt[CELLS * lane + c]; sum += v[c]; }
-                uint32_t x = sum;
-                #pragma unroll
-                for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)lane >= o) x += y; }
-                uint32_t ex = x - sum;
-                #pragma unroll
-                for (int c = 0; c < CELLS; c++) { s_cnt[CELLS * lane + c] = ex; ex += v[c]; }
-            }
-            __syncthreads();
-            s_perm[s_cnt[cls * SHADE_WARPS + warp] + rank] = (uint16_t)(threadIdx.x | (cls << 12));
-            __syncthreads();
-            e = s_perm[threadIdx.x];
+    uint32_t tile = warp_claim(&pv.c->cur_shade, (uint32_t)WTILE);
+    while (tile < n) {
+        // ---- class bytes of this lane's 8 paths (round r: path tile + 32 r + lane), 4 bits each
+        uint32_t cls = 0;
+        #pragma unroll
+        for (int r = 0; r < WROUNDS; r++) {
+            const uint32_t idx = tile + 32u * r + lane;
+            const uint32_t c = idx < n ? (uint32_t)pv.hit_class[pos_at(idx)] & 15u : (uint32_t)Q_HOLE;
+            cls |= c << (4 * r);
         }
-        const int k = (int)(e >> 12);
+        // ---- pass 1: class histogram (lane k < 8 counts class k), paths that continue / end
+        uint32_t hist = 0, nc = 0, nt = 0;
+        #pragma unroll
+        for (int r = 0; r < WROUNDS; r++) {
+            const uint32_t c = (cls >> (4 * r)) & 15u;
+            const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1u), b1 = __ballot_sync(0xffffffffu, c & 2u), b2 = __ballot_sync(0xffffffffu, c & 4u);
+            hist += __popc(class_mask(b0, b1, b2, lane & 7u));
+            nc += __popc(__ballot_sync(0xffffffffu, class_continues(c)));
+            nt += __popc(__ballot_sync(0xffffffffu, class_terminates(c)));
+        }
+        // ---- allocation in pool `next` and the next tile: three INDEPENDENT atomics by lane 0, consumed after pass 2.
+        //      The fresh region needs no counter of its own — samples [iter_begin, next_sample) are regenerated in this
+        //      iteration, so a tile's offset in the region is g0 - iter_begin and k_turnover derives n_fresh from the cursor
+        uint32_t base_b = 0, tile_next = 0;
+        unsigned long long g0 = 0;
+        if (lane == 0) {
+            tile_next = atomicAdd(&pv.c->cur_shade, (uint32_t)WTILE);
+            if (nc) base_b = atomicAdd(&pv.c->n_bounce[next], nc);
+            if (nt) g0 = atomicAdd(&pv.c->next_sample, (unsigned long long)nt);
+        }
+        // ---- pass 2: sorted position of every path = class offset + paths of the class in earlier rounds + rank in the round
+        uint32_t run = hist;                                    // lane k < 8: exclusive prefix over the classes
+        #pragma unroll
+        for (int o = 1; o < 8; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, run, o); if ((lane & 7u) >= (uint32_t)o) run += y; }
+        run -= hist;
+        uint32_t cbase = 0, tbase = 0;
+        #pragma unroll
+        for (int r = 0; r < WROUNDS; r++) {
+            const uint32_t c = (cls >> (4 * r)) & 15u, k = c & 7u;
+            const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1u), b1 = __ballot_sync(0xffffffffu, c & 2u), b2 = __ballot_sync(0xffffffffu, c & 4u);
+            const uint32_t peers = class_mask(b0, b1, b2, k);
+            const uint32_t at = __shfl_sync(0xffffffffu, run, k) + __popc(peers & lt);
+            run += __popc(class_mask(b0, b1, b2, lane & 7u));
+            const bool cont = class_continues(c), term = class_terminates(c);
+            const uint32_t mc = __ballot_sync(0xffffffffu, cont), mt = __ballot_sync(0xffffffffu, term);
+            const uint32_t xr = cont ? cbase + __popc(mc & lt) : tbase + __popc(mt & lt);
+            cbase += __popc(mc); tbase += __popc(mt);
+            perm[at] = (32u * r + lane) | c << 8 | xr << 12;
+        }
+        __syncwarp();
+        base_b = __shfl_sync(0xffffffffu, base_b, 0);
+        tile_next = __shfl_sync(0xffffffffu, tile_next, 0);
+        g0 = __shfl_sync(0xffffffffu, g0, 0);
+        uint32_t n_regen = 0;
+        if (nt && g0 < fp.total_samples) n_regen = (uint32_t)min((unsigned long long)nt, fp.total_samples - g0);
+        const uint32_t base_f = n_regen ? (uint32_t)(g0 - iter_begin) : 0u;
 
-        // -- shade one path
-        bool continues = false, terminated = false;
-        float4 new_o, new_d, new_thr;
-        if (k < NP) {
-            const uint32_t pos = pos_at(tile + (e & 0xfffu));
-            const float4 th = pv.thr[cur][pos];
-            const float4 d = pv.ray_d[cur][pos];
-            const uint32_t pixel = __float_as_uint(th.w), sb = __float_as_uint(d.w);
-            const uint32_t sample = sb & 0xffffffu, bounce = sb >> 24;
-            float3 thr = make_float3(th.x, th.y, th.z);
-            terminated = true;
-            if (k == Q_MISS) {
-                accumulate(fp.accum, pixel, thr * f3(sv.background[0], sv.background[1], sv.background[2]));   // render.h:64
-            } else {
-                const float4 o = pv.ray_o[cur][pos];
-                const uint2 h = pv.hit[pos];
-                Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
-                const int prim = (int)h.y;
-                const float t = __uint_as_float(h.x);
-                HitAttr rec;
-                uint32_t mat;
-                if (prim >= 0) { const DPrim p = sv.prims[prim]; prim_attr(sv, p, r, t, rec); mat = p.material; }
-                else { const DMedium m = sv.media[-2 - prim]; medium_attr(sv, m, r, t, rec); mat = m.material; }
-                const rt_flat_material m = sv.materials[mat];
-                if (m.type == RT_MAT_DIFFUSE_LIGHT) {
-                    accumulate(fp.accum, pixel, thr * texture_value(sv, m.texture, rec.u, rec.v, rec.p));           // render.h:68, :75
-                } else {
-                    const RngKey key{pixel, sample, bounce, fp.seed};
-                    float3 attenuation;
-                    Ray scattered;
-                    if (material_scatter(sv, m, r, rec, key, attenuation, scattered) && bounce + 1 < fp.max_depth) {   // render.h:70-73, :80
-                        thr = thr * attenuation;
-                        new_o = make_float4(scattered.o.x, scattered.o.y, scattered.o.z, scattered.tm);
-                        new_d = make_float4(scattered.d.x, scattered.d.y, scattered.d.z, __uint_as_float(sample | ((bounce + 1) << 24)));
-                        new_thr = make_float4(thr.x, thr.y, thr.z, th.w);
-                        continues = true;
-                        terminated = false;
-                    }
-                    // absorbed (metal scattering into the surface) or depth exhausted: contributes black
+        // ---- shade, a round = 32 paths of (mostly) one class; results go straight to their slots
+        #pragma unroll 1
+        for (int r = 0; r < WROUNDS; r++) {
+            const uint32_t e = perm[32 * r + lane];
+            const uint32_t c = (e >> 8) & 15u, k = c & 7u, xr = e >> 12;
+            if (__all_sync(0xffffffffu, k == (uint32_t)Q_HOLE)) break;      // holes sort last
+            if (k == (uint32_t)Q_HOLE) continue;
+            const uint32_t pos = pos_at(tile + (e & 255u));
+            ShadeOut out;
+            const bool goes_on = shade_path(sv, pv, fp, cur, pos, k, (c & (uint32_t)Q_LAST) != 0, out);
+            if (class_continues(c)) {
+                const uint32_t dst = base_b + xr;                            // survivors keep tile order
+                if (goes_on) { pv.ray_o[next][dst] = out.o; pv.ray_d[next][dst] = out.d; pv.thr[next][dst] = out.thr; }
+                else {   // absorbed after its slot was reserved: a dead slot, counted out of the ray total; its sample slot regenerates one iteration late
+                    pv.ray_d[next][dst] = make_float4(0.f, 0.f, 1.f, __uint_as_float(DEAD_BOUNCE << 24));
+                    pv.ray_o[next][dst] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    atomicAdd(&pv.c->n_dead[next].n, 1u);
                 }
-            }
+            } else if (xr < n_regen) start_path(sv, pv, fp, next, pv.capacity - (base_f + n_regen) + xr, g0 + xr);
         }
-
-        // -- block-aggregated allocation in pool `next`: survivors at the bottom (tile order kept), regenerated
-        //    camera paths (the next samples of the global cursor) at the top; the next tile is claimed here too
-        const uint32_t mc = __ballot_sync(0xffffffffu, continues), mt = __ballot_sync(0xffffffffu, terminated);
-        if (lane == 0) { s_wcont[warp] = __popc(mc); s_wterm[warp] = __popc(mt); }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            uint32_t nc = 0, nt = 0;
-            #pragma unroll
-            for (int w = 0; w < SHADE_WARPS; w++) {
-                const uint32_t a = s_wcont[w], b = s_wterm[w];
-                s_wcont[w] = nc; s_wterm[w] = nt;           // exclusive prefixes
-                nc += a; nt += b;
-            }
-            // three INDEPENDENT atomics (one round trip, not three): the fresh region needs no counter of its own —
-            // samples [iter_begin, next_sample) are regenerated in this iteration, so a block's offset in the region
-            // is g0 - iter_begin and k_turnover derives n_fresh from the cursor
-            const uint32_t tile_next = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
-            const uint32_t base_b = nc ? atomicAdd(&pv.c->n_bounce[next], nc) : 0u;
-            const unsigned long long g0 = nt ? atomicAdd(&pv.c->next_sample, (unsigned long long)nt) : 0ull;
-            uint32_t n_regen = 0;
-            if (nt && g0 < fp.total_samples) n_regen = (uint32_t)min((unsigned long long)nt, fp.total_samples - g0);
-            s_base_b = base_b;
-            s_base_f = n_regen ? (uint32_t)(g0 - iter_begin) : 0u;
-            s_nregen = n_regen;
-            s_g0 = g0;
-            s_tile[it ^ 1] = tile_next;
-        }
-        __syncthreads();
-        const uint32_t tile_next = s_tile[it ^ 1];
-        const int cls_next = class_of(tile_next);    // in flight while this tile's results are stored
-        if (continues) {
-            const uint32_t dst = s_base_b + s_wcont[warp] + __popc(mc & lt);
-            pv.ray_o[next][dst] = new_o;
-            pv.ray_d[next][dst] = new_d;
-            pv.thr[next][dst] = new_thr;
-        }
-        if (terminated) {
-            const uint32_t r = s_wterm[warp] + __popc(mt & lt);
-            if (r < s_nregen) start_path(sv, pv, fp, next, pv.capacity - (s_base_f + s_nregen) + r, s_g0 + r);
-        }
+        __syncwarp();
         tile = tile_next;
-        cls = cls_next;
     }
 }
 
-template <int SHADE_BLOCK>
-__global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_tiles<SHADE_BLOCK, false>(sv, pv, fp, cur); }
-// shade of the deferred extend: holes (Q_SUSP) in the tiles and the finished-resumed region behind the pool; held to the 64 registers the plain kernel gets
-__global__ void __launch_bounds__(256, 4) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_tiles<256, true>(sv, pv, fp, cur); }
+__global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<false>(sv, pv, fp, cur); }
+// shade of the deferred extend: holes in the tiles and the finished-resumed region behind the pool
+__global__ void __launch_bounds__(SHADE_BLOCK) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<true>(sv, pv, fp, cur); }
 
-// ---- turnover -------------------------------------------------------------------------------------
-__global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out) {
-    Counters* c = pv.c;
-    c->total_rays += c->n_bounce[cur] + c->n_fresh[cur];
-    c->n_bounce[cur] = 0; c->n_fresh[cur] = 0;
-    const unsigned long long started = min(c->next_sample, total_samples);   // samples regenerated by this iteration's shade
-    c->n_fresh[cur ^ 1] = (uint32_t)(started - c->iter_begin);
-    c->iter_begin = started;
-    c->cur_extend = 0; c->cur_shade = 0;
-    c->cont[cur ^ 1].n = 0;       // consumed by this iteration's extend; the next iteration's extend appends to it
-    c->n_fin[cur].n = 0;
-    *live_out = c->n_bounce[cur ^ 1] + c->n_fresh[cur ^ 1] + c->cont[cur].n;   // + the suspended paths the next extend resumes
-}
-
-__global__ void k_scale(const float* sums, float* out, size_t n, float scale) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = scale * sums[i];      // col / float(ns) = (1/ns) * col, render.h:112 + vec3.h:117
-}
-
-uint32_t suspend_threshold(const DeviceScene& ds) {
-    if (const char* e = getenv("RT_SUSPEND")) return (uint32_t)std::min(std::max(atoi(e), 0), 31);
-    return ds.view.n_prims >= SUSPEND_MIN_PRIMS ? SUSPEND_BELOW_DEFAULT : 0u;
-}
-
-// `owner`: where the pool is kept (DeviceScene::pool, or RenderPool::second for the second lane); set before the first
-// allocation so that a failure is cleaned up with the scene.
-int pool_create(DeviceScene& ds, RenderPool** owner, uint32_t capacity, int lanes) {
-    RenderPool* p = new RenderPool;
-    p->device = ds.device;
-    p->v.capacity = capacity;
-    p->lanes = lanes;
-    *owner = p;
-    // Deferred extend: a whole warp suspends its stragglers once <= suspend_below lanes are live.  On by default for scenes
-    // whose walks are long and uneven — above SUSPEND_MIN_PRIMS primitives, i.e. triangle meshes: 1 M triangles +7.8 %
-    // (lane utilisation of the node loop 0.42 -> 0.61-0.68, extend -11 %) — and off where the node loop is already
-    // 0.64-0.87 full (every scene the reference ships: the holes suspended paths leave in the shade tiles cost more than
-    // extend gains; profiles/r01_v9_experiments.md).  RT_SUSPEND=n forces a threshold, 0 = off.
-    p->suspend_below = suspend_threshold(ds);
-    const size_t slots = p->suspend_below ? 2 * (size_t)capacity : capacity;   // + the suspended region at positions >= capacity
-    for (int b = 0; b < 2; b++) {
-        RT_CUDA(cudaMalloc(&p->v.ray_o[b], sizeof(float4) * slots));
-        RT_CUDA(cudaMalloc(&p->v.ray_d[b], sizeof(float4) * slots));
-        RT_CUDA(cudaMalloc(&p->v.thr[b], sizeof(float4) * slots));
-    }
-    RT_CUDA(cudaMalloc(&p->v.hit, sizeof(uint2) * slots));
-    RT_CUDA(cudaMalloc(&p->v.hit_class, sizeof(uint8_t) * slots));
-    RT_CUDA(cudaMalloc(&p->v.c, sizeof(Counters)));
-    RT_CUDA(cudaHostAlloc(&p->h_live, sizeof(uint32_t) * POLL_SLOTS, cudaHostAllocMapped));
-    RT_CUDA(cudaHostAlloc(&p->h_counters, sizeof(Counters), cudaHostAllocDefault));
-    for (auto& e : p->poll_ev) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    RT_CUDA(cudaEventCreate(&p->ev_begin)); RT_CUDA(cudaEventCreate(&p->ev_end));
-    RT_CUDA(cudaEventCreateWithFlags(&p->ev_extend, cudaEventDisableTiming));
-    RT_CUDA(cudaStreamCreateWithFlags(&p->capture_stream, cudaStreamNonBlocking));
-    int sms = 0;
-    RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
-    int occ = 0;
-    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend<false, true>, EXTEND_BLOCK, 0));
-    p->grid_extend = sms * std::max(occ, 1);
-    p->shade_block = (getenv("RT_EXP") && (atoi(getenv("RT_EXP")) & 8)) ? 128 : (getenv("RT_EXP") && (atoi(getenv("RT_EXP")) & 64)) ? 512 : 256;
-    if (p->shade_block == 128) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<128>, 128, 0));
-    else if (p->shade_block == 512) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<512>, 512, 0));
-    else RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade<256>, 256, 0));
-    p->grid_shade = sms * std::max(occ, 1);
-    if (p->suspend_below) {
-        for (int b = 0; b < 2; b++) {
-            RT_CUDA(cudaMalloc(&p->v.cont_walk[b], sizeof(uint4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_o[b], sizeof(float4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_d[b], sizeof(float4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_thr[b], sizeof(float4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_sp[b], sizeof(uint8_t) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_stack[b], sizeof(int) * (size_t)capacity * RT_SUSPEND_STACK));
-        }
-        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend_defer<false>, EXTEND_BLOCK, 0));
-        p->grid_extend = sms * std::max(occ, 1);
-        RT_CUDA((cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_defer, 256, 0)));
-        p->grid_shade = sms * std::max(occ, 1);
-        p->shade_block = 256;
-    }
-    if (lanes > 1) {
-        // two lanes share the SMs: the persistent grids are sized so that one lane's extend and the other lane's shade
-        // are resident together (RT_LANE_GRID="extend blocks per SM,shade blocks per SM")
-        int eb = 6, sb = 1;
-        if (const char* e = getenv("RT_LANE_GRID")) sscanf(e, "%d,%d", &eb, &sb);
-        p->grid_extend = sms * std::max(1, std::min(eb, p->grid_extend / sms));
-        p->grid_shade = sms * std::max(1, std::min(sb, p->grid_shade / sms));
-    }
-    if (const char* e = getenv("RT_GRID_DIV")) {   // experiment: several renders sharing one GPU (tools/overlap_probe.py)
-        const int div = std::max(1, atoi(e));
-        p->grid_extend = std::max(sms, p->grid_extend / div);
-        p->grid_shade = std::max(sms, p->grid_shade / div);
-    }
-    return RT_OK;
-}
-
-// One wavefront pipeline of a frame: its pools, its share of the samples, its stream.
-struct LaneRun {
-    RenderPool* P = nullptr;
-    FrameParams fp{};
-    cudaStream_t stream = nullptr;
-    uint32_t* d_live = nullptr;
-    uint64_t it = 0, launches = 0, iterations = 0, max_iterations = 0;
-    size_t n_timer = 0;
-    bool done = false;
-};
-
-int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, cudaStream_t stream, rt_render_stats* stats) {
-    if (st.width == 0 || st.height == 0 || st.samples_per_pixel == 0 || st.max_depth == 0 || st.max_depth > 255) {
-        set_error("render: width/height/samples_per_pixel must be > 0 and 1 <= max_depth <= 255");
-        return RT_ERR_INVALID;
-    }
-    const uint32_t s_first = st.sample_first;
-    const uint32_t s_count = st.sample_count ? st.sample_count : st.samples_per_pixel - std::min(st.samples_per_pixel, s_first);
-    if ((unsigned long long)s_first + s_count > 0xffffffull) { set_error("render: sample index exceeds 2^24"); return RT_ERR_INVALID; }
-    RT_CUDA(cudaSetDevice(ds.device));
-    const unsigned long long frame_pix = (unsigned long long)st.width * st.height;
-    if (frame_pix >= (1ull << 32)) { set_error("render: more than 2^32 pixels"); return RT_ERR_INVALID; }
-    unsigned long long npix = frame_pix;
-    const uint32_t tile_count = st.tile_count > 1 ? st.tile_count : 1u;
-    if (st.tile_index >= tile_count) { set_error("render: tile_index >= tile_count"); return RT_ERR_INVALID; }
-    if (tile_count > 1) {   // pixels in the film blocks this call owns; only the last block of the frame can be short
-        const unsigned long long nb = (frame_pix + RT_TILE_BLOCK_PIXELS - 1) / RT_TILE_BLOCK_PIXELS;
-        const unsigned long long owned = nb > st.tile_index ? (nb - st.tile_index + tile_count - 1) / tile_count : 0;
-        npix = owned * RT_TILE_BLOCK_PIXELS;
-        if (owned && (owned - 1) * tile_count + st.tile_index == nb - 1) npix -= nb * RT_TILE_BLOCK_PIXELS - frame_pix;
-    }
-    const unsigned long long total = npix * s_count;
-    // Two lanes (RT_LANES=2): the sample range is cut in two and each half runs as its own wavefront pipeline — pools,
-    // counters, stream — into the same accumulation buffer.  The lanes' extend kernels are chained by events so that they
-    // alternate, which leaves one lane's latency-bound shade running beside the other lane's extend.  Which lane traces a
-    // sample does not change it (Philox keys), so the image is the same up to the order of the float atomics.
-    int lanes = getenv("RT_LANES") ? std::min(2, std::max(1, atoi(getenv("RT_LANES")))) : 1;
-    if (s_count < 2 || total < (1ull << 16)) lanes = 1;
-    uint32_t capacity = st.pool_paths ? st.pool_paths : (1u << 22);
-    capacity = (uint32_t)std::min<unsigned long long>(capacity, std::max<unsigned long long>((total + lanes - 1) / lanes, 32ull));
-    capacity = (capacity + 31u) & ~31u;
-    if (ds.pool && (ds.pool->v.capacity != capacity || ds.pool->lanes != lanes || ds.pool->suspend_below != suspend_threshold(ds))) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
-    if (!ds.pool) {
-        int rc = pool_create(ds, &ds.pool, capacity, lanes);
-        if (rc < 0) return rc;
-        if (lanes > 1) {
-            rc = pool_create(ds, &ds.pool->second, capacity, lanes);
-            if (rc < 0) return rc;
-            RT_CUDA(cudaStreamCreateWithFlags(&ds.pool->second->own_stream, cudaStreamNonBlocking));
-        }
-    }
-    const bool count = (st.flags & RT_RENDER_COUNTERS) != 0;
-    const bool timers = (st.flags & RT_RENDER_TIMERS) != 0;
-    const uint32_t exp_bits = (uint32_t)(getenv("RT_EXP") ? atoi(getenv("RT_EXP")) : 0);
-
-    LaneRun run[2];
-    uint32_t first = s_first;
-    for (int l = 0; l < lanes; l++) {
-        LaneRun& L = run[l];
-        L.P = l ? ds.pool->second : ds.pool;
-        L.stream = l ? L.P->own_stream : stream;
-        const uint32_t share = lanes == 1 ? s_count : (l == 0 ? (s_count + 1) / 2 : s_count / 2);
-        const unsigned long long lane_total = npix * share;
-        const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
-        L.fp = FrameParams{st.width, st.height, st.max_depth, st.seed, first, exp_bits, lane_total, npix, magic, d_accum, st.tile_index, tile_count};
-        first += share;
-        // hard bound: every iteration with live paths retires >= 1 segment of a path of <= max_depth segments
-        // (deferred extend: a suspended walk advances by at least one leaf phase per iteration, and only whole warps suspend)
-        L.max_iterations = ((lane_total / capacity + 2) * (uint64_t)st.max_depth + POLL_DEPTH + 64) * (L.P->suspend_below ? 64u : 1u);
-        RT_CUDA(cudaHostGetDevicePointer(&L.d_live, L.P->h_live, 0));
-        L.done = lane_total == 0;
-    }
-    auto tick = [&](LaneRun& L) -> int {   // records the lane's next timer event on its stream
-        if (!timers) return RT_OK;
-        RenderPool& P = *L.P;
-        if (L.n_timer == P.timer_ev.size()) { cudaEvent_t e; RT_CUDA(cudaEventCreate(&e)); P.timer_ev.push_back(e); }
-        RT_CUDA(cudaEventRecord(P.timer_ev[L.n_timer++], L.stream));
-        return RT_OK;
-    };
-
-    RenderPool& P0 = *ds.pool;
-    RT_CUDA(cudaEventRecord(P0.ev_begin, stream));
-    for (int l = 0; l < lanes; l++) {
-        LaneRun& L = run[l];
-        if (l) RT_CUDA(cudaStreamWaitEvent(L.stream, P0.ev_begin, 0));   // the caller's stream orders the buffer before this call
-        RT_CUDA(cudaMemsetAsync(L.P->v.c, 0, sizeof(Counters), L.stream));
-        if (L.done) continue;
-        // frame start: the first min(capacity, total) samples fill pool 0
-        const uint32_t n0 = (uint32_t)std::min<unsigned long long>(capacity, L.fp.total_samples);
-        k_generate<<<(n0 + 255) / 256, 256, 0, L.stream>>>(ds.view, L.P->v, L.fp, n0);
-        L.launches += 1;
-    }
-    // the three launches of one iteration (cur = parity of the iteration, slot = where turnover publishes the live count)
-    auto launch_iteration = [&](LaneRun& L, int cur, uint32_t slot, cudaStream_t s, bool timed) -> int {
-        RenderPool& P = *L.P;
-        if (timed && tick(L) < 0) return RT_ERR_CUDA;
-        if (P.suspend_below) {
-            if (count) k_extend_defer<true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
-            else k_extend_defer<false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur, P.suspend_below);
-        } else if (exp_bits & 16u) {   // RT_EXP=16: streaming refill
-            if (count) k_extend_stream<true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
-            else k_extend_stream<false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
-        } else if (count) k_extend<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
-        else if (exp_bits & 4u) k_extend<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);   // RT_EXP=4: fused loop
-        else k_extend<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, L.fp, cur);
-        if (lanes > 1) RT_CUDA(cudaEventRecord(P.ev_extend, s));
-        if (timed && tick(L) < 0) return RT_ERR_CUDA;
-        if (P.suspend_below) k_shade_defer<<<P.grid_shade, 256, 0, s>>>(ds.view, P.v, L.fp, cur);
-        else if (P.shade_block == 128) k_shade<128><<<P.grid_shade, 128, 0, s>>>(ds.view, P.v, L.fp, cur);
-        else if (P.shade_block == 512) k_shade<512><<<P.grid_shade, 512, 0, s>>>(ds.view, P.v, L.fp, cur);   // RT_EXP=64
-        else k_shade<256><<<P.grid_shade, 256, 0, s>>>(ds.view, P.v, L.fp, cur);
-        if (timed && tick(L) < 0) return RT_ERR_CUDA;
-        k_turnover<<<1, 1, 0, s>>>(P.v, cur, L.fp.total_samples, L.d_live + slot);
-        return RT_OK;
-    };
-    // One lane, no per-kernel timers: GRAPH_ITERS iterations go to the GPU as ONE CUDA graph.  Small frames and the drain of
-    // every frame are launch-bound (3 launches of a few microseconds per iteration); the graph takes the host out of that
-    // loop.  The graph is captured per call (the frame parameters are kernel arguments) and swapped into the pool's
-    // instantiated graph with cudaGraphExecUpdate — same topology, no re-instantiation.  The host stays one graph ahead of
-    // the live count it reads, so a finished frame costs at most one graph of empty iterations.
-    const bool use_graph = lanes == 1 && !timers && !run[0].done && !getenv("RT_NO_GRAPH");
-    if (use_graph) {
-        LaneRun& L = run[0];
-        RenderPool& P = *L.P;
-        constexpr int GRAPH_ITERS = POLL_SLOTS;     // a whole period of (parity, live-count slot)
-        cudaGraph_t g = nullptr;
-        RT_CUDA(cudaStreamBeginCapture(P.capture_stream, cudaStreamCaptureModeThreadLocal));
-        int rc = RT_OK;
-        for (int k = 0; k < GRAPH_ITERS && rc == RT_OK; k++) rc = launch_iteration(L, k & 1, (uint32_t)k, P.capture_stream, false);
-        const cudaError_t ce = cudaStreamEndCapture(P.capture_stream, &g);
-        if (rc < 0 || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); cudaGetLastError(); set_error("render: graph capture failed"); return RT_ERR_CUDA; }
-        if (P.graph_exec) {
-            cudaGraphExecUpdateResultInfo info;
-            if (cudaGraphExecUpdate(P.graph_exec, g, &info) != cudaSuccess) { cudaGetLastError(); cudaGraphExecDestroy(P.graph_exec); P.graph_exec = nullptr; }
-        }
-        if (!P.graph_exec && cuda_fail(cudaGraphInstantiate(&P.graph_exec, g, 0), "cudaGraphInstantiate", __FILE__, __LINE__)) { cudaGraphDestroy(g); return RT_ERR_CUDA; }
-        cudaGraphDestroy(g);
-        for (uint64_t gi = 0; !L.done; gi++) {
-            RT_CUDA(cudaGraphLaunch(P.graph_exec, stream));
-            RT_CUDA(cudaEventRecord(P.poll_ev[gi & 1], stream));
-            L.launches += 3 * GRAPH_ITERS; L.iterations += GRAPH_ITERS; L.it += GRAPH_ITERS;
-            if (gi >= 1) {   // the graph before this one: its last iteration's live count (a later one is as good: zero stays zero)
-                RT_CUDA(cudaEventSynchronize(P.poll_ev[(gi - 1) & 1]));
-                if (P.h_live[GRAPH_ITERS - 1] == 0) L.done = true;
-            }
-            if (L.it > L.max_iterations + 2 * GRAPH_ITERS) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
-        }
-    }
-    for (bool all_done = use_graph; !all_done;) {
-        all_done = true;
-        for (int l = 0; l < lanes; l++) {
-            LaneRun& L = run[l];
-            if (L.done) continue;
-            all_done = false;
-            RenderPool& P = *L.P;
-            // two lanes: this extend starts when the other lane's latest extend has finished, so the two alternate
-            if (lanes > 1 && run[l ^ 1].it > 0) RT_CUDA(cudaStreamWaitEvent(L.stream, run[l ^ 1].P->ev_extend, 0));
-            const int rc = launch_iteration(L, (int)(L.it & 1), (uint32_t)(L.it % POLL_SLOTS), L.stream, true);
-            if (rc < 0) return rc;
-            RT_CUDA(cudaEventRecord(P.poll_ev[L.it % POLL_SLOTS], L.stream));
-            L.launches += 3;
-            L.iterations++;
-            if (L.it >= POLL_DEPTH) {
-                const uint64_t old = L.it - POLL_DEPTH;
-                RT_CUDA(cudaEventSynchronize(P.poll_ev[old % POLL_SLOTS]));
-                if (P.h_live[old % POLL_SLOTS] == 0) L.done = true;
-            }
-            if (L.it > L.max_iterations) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
-            L.it++;
-        }
-    }
-    for (int l = 0; l < lanes; l++) {
-        LaneRun& L = run[l];
-        if (tick(L) < 0) return RT_ERR_CUDA;
-        RT_CUDA(cudaMemcpyAsync(L.P->h_counters, L.P->v.c, sizeof(Counters), cudaMemcpyDeviceToHost, L.stream));
-        if (l) {   // the caller's stream continues after the second lane
-            RT_CUDA(cudaEventRecord(L.P->ev_end, L.stream));
-            RT_CUDA(cudaStreamWaitEvent(stream, L.P->ev_end, 0));
-        }
-    }
-    RT_CUDA(cudaEventRecord(P0.ev_end, stream));
-    RT_CUDA(cudaStreamSynchronize(stream));
-    RT_CUDA(cudaGetLastError());
-    if (stats) {
-        std::memset(stats, 0, sizeof(*stats));
-        double ext = 0, shd = 0, fin = 0;
-        float ms_gen = 0.f;
-        for (int l = 0; l < lanes; l++) {
-            LaneRun& L = run[l];
-            const Counters& c = *L.P->h_counters;
-            stats->samples += std::min<unsigned long long>(c.next_sample, L.fp.total_samples);
-            stats->rays += c.total_rays;
-            stats->iterations += L.iterations;
-            stats->kernel_launches += L.launches;
-            stats->nodes_visited += c.nodes;
-            stats->prim_tests += c.prim_tests;
-            stats->node_slots += c.node_slots;
-            if (timers) {   // per-kernel device time, summed over the iterations of this frame: 3 events per iteration + 1
-                            // (two lanes: the intervals of the lanes overlap in time; the sums say what each kernel occupied)
-                const std::vector<cudaEvent_t>& ev = L.P->timer_ev;
-                for (size_t k = 0; k + 3 < L.n_timer; k += 3) {
-                    float a = 0, b = 0, d = 0;
-                    cudaEventElapsedTime(&a, ev[k], ev[k + 1]);
-                    cudaEventElapsedTime(&b, ev[k + 1], ev[k + 2]);
-                    cudaEventElapsedTime(&d, ev[k + 2], ev[k + 3]);
-                    ext += a; shd += b; fin += d;
-                }
-                if (l == 0 && L.n_timer) cudaEventElapsedTime(&ms_gen, P0.ev_begin, ev[0]);
-            }
-        }
-        cudaEventElapsedTime(&stats->ms_total, P0.ev_begin, P0.ev_end);
-        stats->ms_extend = (float)ext; stats->ms_shade = (float)shd; stats->ms_generate = ms_gen; stats->ms_finish = (float)fin;
-    }
-    return RT_OK;
-}
-
-} // namespace
-} // namespace rtb
-
-using namespace rtb;
-
-extern "C" int rt_render_device(rt_scene* s, const rt_render_settings* st, float* d_accum, void* cuda_stream, rt_render_stats* stats) {
-    if (!s || !st || !d_accum) { set_error("render: bad argument"); return RT_ERR_INVALID; }
-    DeviceScene* ds = device_of(s);
-    if (!ds) { set_error("render: scene not committed (rt_scene_commit)"); return RT_ERR_STATE; }
-    return render_impl(*ds, *st, d_accum, (cudaStream_t)cuda_stream, stats);
-}
-
-extern "C" int rt_render(rt_scene* s, const rt_render_settings* st, float* out_rgb, rt_render_stats* stats) {
-    if (!s || !st || !out_rgb) { set_error("render: bad argument"); return RT_ERR_INVALID; }
-    DeviceScene* ds = device_of(s);
-    if (!ds) { set_error("render: scene not committed (rt_scene_commit)"); return RT_ERR_STATE; }
-    RT_CUDA(cudaSetDevice(ds->device));
-    const size_t n = (size_t)st->width * st->height * 3;
-    float* d_accum = nullptr;
-    RT_CUDA(cudaMalloc(&d_accum, sizeof(float) * n));
-    const bool accumulate = (st->flags & RT_RENDER_ACCUMULATE) != 0;   // progressive: out_rgb carries the sums so far
-    if (accumulate) RT_CUDA(cudaMemcpyAsync(d_accum, out_rgb, sizeof(float) * n, cudaMemcpyHostToDevice, 0));
-    else RT_CUDA(cudaMemsetAsync(d_accum, 0, sizeof(float) * n, 0));
-    const int rc = render_impl(*ds, *st, d_accum, 0, stats);
-    if (rc < 0) { cudaFree(d_accum); return rc; }
-    if (!accumulate) {
-        const uint32_t s_count = st->sample_count ? st->sample_count : st->samples_per_pixel - std::min(st->samples_per_pixel, st->sample_first);
-        k_scale<<<(unsigned)((n + 255) / 256), 256>>>(d_accum, d_accum, n, 1 / (float)s_count);
-    }
-    RT_CUDA(cudaMemcpy(out_rgb, d_accum, sizeof(float) * n, cudaMemcpyDeviceToHost));
-    cudaFree(d_accum);
-    return RT_OK;
-}
