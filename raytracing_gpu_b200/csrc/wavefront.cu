@@ -509,3 +509,137 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv
 // shade of the deferred extend: holes in the tiles and the finished-resumed region behind the pool
 __global__ void __launch_bounds__(SHADE_BLOCK) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<true>(sv, pv, fp, cur); }
 
+// Round 1's shade, kept for the same-box A/B (RT_DEBUG_BLOCK_SHADE): a BLOCK sorts a 256-path tile by class in shared
+// memory, thread 0 allocates between two barriers — five __syncthreads per tile.
+template <bool DEFER>
+__device__ __forceinline__ void shade_block_tiles(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
+    constexpr int NC = 8;
+    __shared__ uint32_t s_tile[2];                   // this tile / the next one (claimed while this one is shaded)
+    constexpr int CELLS = 2;                         // class-table cells per lane of the scanning warp
+    __shared__ uint32_t s_cnt[32 * CELLS];           // [class][warp] counts -> exclusive offsets
+    __shared__ uint16_t s_perm[SHADE_BLOCK];         // sorted rank -> tile-local index | class << 12
+    __shared__ uint32_t s_wcont[SHADE_WARPS], s_wterm[SHADE_WARPS];
+    __shared__ uint32_t s_base_b, s_base_f, s_nregen;
+    __shared__ unsigned long long s_g0;
+    static_assert(NC * SHADE_WARPS <= 32 * CELLS, "class table must fit one warp scan");
+    const int next = cur ^ 1;
+    const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
+    const uint32_t n = n_pool + (DEFER ? pv.c->n_fin[cur].n : 0u);
+    const unsigned long long iter_begin = pv.c->iter_begin;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    auto pos_at = [&](uint32_t idx) { return DEFER && idx >= n_pool ? pv.capacity + (idx - n_pool) : pos_of(idx, n_b, n_pool, pv.capacity); };
+    if (threadIdx.x < 32 * CELLS) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) s_tile[0] = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
+    __syncthreads();
+    auto class_of = [&](uint32_t tile) {
+        const uint32_t idx = tile + threadIdx.x;
+        return idx < n ? (int)(pv.hit_class[pos_at(idx)] & 15u) : (int)Q_HOLE;
+    };
+    uint32_t tile = s_tile[0];
+    int cls = class_of(tile);
+    for (int it = 0;; it ^= 1) {
+        if (tile >= n) break;
+        uint32_t rank = 0;
+        #pragma unroll
+        for (int k = 0; k < NC; k++) {
+            const uint32_t m = __ballot_sync(0xffffffffu, (cls & 7) == k);
+            if ((cls & 7) == k) rank = __popc(m & lt);
+            if ((int)lane == k) s_cnt[k * SHADE_WARPS + warp] = __popc(m);
+        }
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t v[CELLS], sum = 0;
+            #pragma unroll
+            for (int c = 0; c < CELLS; c++) { v[c] = s_cnt[CELLS * lane + c]; sum += v[c]; }
+            uint32_t x = sum;
+            #pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)lane >= o) x += y; }
+            uint32_t ex = x - sum;
+            #pragma unroll
+            for (int c = 0; c < CELLS; c++) { s_cnt[CELLS * lane + c] = ex; ex += v[c]; }
+        }
+        __syncthreads();
+        s_perm[s_cnt[(cls & 7) * SHADE_WARPS + warp] + rank] = (uint16_t)(threadIdx.x | (cls << 12));
+        __syncthreads();
+        const uint32_t e = s_perm[threadIdx.x];
+        const uint32_t c = e >> 12, k = c & 7u;
+        bool continues = false, terminated = false;
+        ShadeOut out;
+        if (k != (uint32_t)Q_HOLE) {
+            continues = shade_path(sv, pv, fp, cur, pos_at(tile + (e & 0xfffu)), k, (c & (uint32_t)Q_LAST) != 0, out);
+            terminated = !continues;
+        }
+        const uint32_t mc = __ballot_sync(0xffffffffu, continues), mt = __ballot_sync(0xffffffffu, terminated);
+        if (lane == 0) { s_wcont[warp] = __popc(mc); s_wterm[warp] = __popc(mt); }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t nc = 0, nt = 0;
+            #pragma unroll
+            for (int w = 0; w < SHADE_WARPS; w++) {
+                const uint32_t a = s_wcont[w], b = s_wterm[w];
+                s_wcont[w] = nc; s_wterm[w] = nt;           // exclusive prefixes
+                nc += a; nt += b;
+            }
+            const uint32_t tile_next = atomicAdd(&pv.c->cur_shade, (uint32_t)SHADE_BLOCK);
+            const uint32_t base_b = nc ? atomicAdd(&pv.c->n_bounce[next], nc) : 0u;
+            const unsigned long long g0 = nt ? atomicAdd(&pv.c->next_sample, (unsigned long long)nt) : 0ull;
+            uint32_t n_regen = 0;
+            if (nt && g0 < fp.total_samples) n_regen = (uint32_t)min((unsigned long long)nt, fp.total_samples - g0);
+            s_base_b = base_b;
+            s_base_f = n_regen ? (uint32_t)(g0 - iter_begin) : 0u;
+            s_nregen = n_regen;
+            s_g0 = g0;
+            s_tile[it ^ 1] = tile_next;
+        }
+        __syncthreads();
+        const uint32_t tile_next = s_tile[it ^ 1];
+        const int cls_next = class_of(tile_next);    // in flight while this tile's results are stored
+        if (continues) {
+            const uint32_t dst = s_base_b + s_wcont[warp] + __popc(mc & lt);
+            pv.ray_o[next][dst] = out.o; pv.ray_d[next][dst] = out.d; pv.thr[next][dst] = out.thr;
+        }
+        if (terminated) {
+            const uint32_t r = s_wterm[warp] + __popc(mt & lt);
+            if (r < s_nregen) start_path(sv, pv, fp, next, pv.capacity - (s_base_f + s_nregen) + r, s_g0 + r);
+        }
+        tile = tile_next;
+        cls = cls_next;
+    }
+}
+__global__ void __launch_bounds__(SHADE_BLOCK) k_shade_block(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_block_tiles<false>(sv, pv, fp, cur); }
+__global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_block_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_block_tiles<true>(sv, pv, fp, cur); }
+
+// ---- turnover -------------------------------------------------------------------------------------
+__global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out) {
+    Counters* c = pv.c;
+    c->total_rays += c->n_bounce[cur] + c->n_fresh[cur] - c->n_dead[cur].n;
+    c->n_bounce[cur] = 0; c->n_fresh[cur] = 0; c->n_dead[cur].n = 0;
+    const unsigned long long started = min(c->next_sample, total_samples);   // samples regenerated by this iteration's shade
+    c->n_fresh[cur ^ 1] = (uint32_t)(started - c->iter_begin);
+    c->iter_begin = started;
+    c->cur_extend = 0; c->cur_shade = 0;
+    c->cont[cur ^ 1].n = 0;       // consumed by this iteration's extend; the next iteration's extend appends to it
+    c->n_fin[cur].n = 0;
+    *live_out = c->n_bounce[cur ^ 1] + c->n_fresh[cur ^ 1] + c->cont[cur].n;   // + the suspended paths the next extend resumes
+}
+
+__global__ void k_scale(const float* sums, float* out, size_t n, float scale) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = scale * sums[i];      // col / float(ns) = (1/ns) * col, render.h:112 + vec3.h:117
+}
+
+// FP32 peak probe (rt_measure_fp32_peak): 8 independent FMA chains per thread, operands the compiler cannot fold
+__global__ void __launch_bounds__(256) k_fma_peak(float* out, float a, float b, int iters) {
+    float x0 = threadIdx.x, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
+    #pragma unroll 1
+    for (int i = 0; i < iters; i++) {
+        #pragma unroll
+        for (int k = 0; k < 16; k++) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
