@@ -186,7 +186,7 @@ int rt_draw(rt_scene* scene, const rt_draw_settings* st, const char* png_path, u
         if (h <= 0) return fail(RT_ERR_INVALID, "draw: computed image height is not positive");
         height = (uint32_t)h;
     }
-    if (!device_of(scene)) { const int rc = rt_scene_commit(scene, (int)st->device, nullptr); if (rc < 0) return rc; }
+    if (!device_scene_is_current(scene)) { const int rc = rt_scene_commit(scene, (int)st->device, nullptr); if (rc < 0) return rc; }   // draw() takes the scene as it is now
     const size_t n = (size_t)width * height * 3;
     std::vector<float> fb(n);
     std::vector<uint8_t> frames(n * no_fb), final_px(n);

@@ -643,3 +643,327 @@ __global__ void __launch_bounds__(256) k_fma_peak(float* out, float a, float b, 
     out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
 }
 
+// Deferred extend: a whole warp suspends its stragglers once <= suspend_below lanes are live.  On by default for scenes
+// whose walks are long and uneven — above SUSPEND_MIN_PRIMS primitives, i.e. triangle meshes: 1 M triangles +7.8 %
+// (lane utilisation of the node loop 0.42 -> 0.61-0.68, extend -11 %) — and off where the node loop is already
+// 0.64-0.87 full (every scene the reference ships: the holes suspended paths leave in the shade tiles cost more than
+// extend gains; profiles/r01_v9_experiments.md).  rt_render_settings::extend_defer overrides.
+uint32_t suspend_threshold(const DeviceScene& ds, const rt_render_settings& st) {
+    if (st.extend_defer == RT_DEFER_OFF) return 0u;
+    if (st.extend_defer >= 2u) return std::min(st.extend_defer - 1u, 31u);
+    return ds.view.n_prims >= SUSPEND_MIN_PRIMS ? SUSPEND_BELOW_DEFAULT : 0u;
+}
+
+// traversal variant of k_extend: the caller's, else the default; the shared-memory stack only for trees it can hold
+int extend_variant(const DeviceScene& ds, const rt_render_settings& st) {
+    int v = (st.traversal & RT_TRAVERSAL_FORCE) ? (int)(st.traversal & 7u) : (int)RT_TRAVERSAL_DEFAULT_BITS;
+    if (ds.build.bvh_depth == 0 || ds.build.bvh_depth + 1 > RT_SHORT_STACK) v &= ~TV_SMEM;
+    return v;
+}
+
+template <bool COUNT> void launch_extend(int v, int grid, cudaStream_t s, const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
+    switch (v) {
+    case 0: k_extend<COUNT, 0><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 1: k_extend<COUNT, 1><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 2: k_extend<COUNT, 2><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 3: k_extend<COUNT, 3><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 4: k_extend<COUNT, 4><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 5: k_extend<COUNT, 5><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 6: k_extend<COUNT, 6><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    default: k_extend<COUNT, 7><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    }
+}
+int extend_occupancy(int v, int* occ) {
+    switch (v) {
+    case 0: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 0>, EXTEND_BLOCK, 0)); break;
+    case 1: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 1>, EXTEND_BLOCK, 0)); break;
+    case 2: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 2>, EXTEND_BLOCK, 0)); break;
+    case 3: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 3>, EXTEND_BLOCK, 0)); break;
+    case 4: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 4>, EXTEND_BLOCK, 0)); break;
+    case 5: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 5>, EXTEND_BLOCK, 0)); break;
+    case 6: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 6>, EXTEND_BLOCK, 0)); break;
+    default: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 7>, EXTEND_BLOCK, 0)); break;
+    }
+    return RT_OK;
+}
+
+int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
+    RenderPool* p = new RenderPool;
+    p->device = ds.device;
+    p->v.capacity = capacity;
+    ds.pool = p;                                  // owned by the scene from here on: a failure below is cleaned up with it
+    p->suspend_below = suspend_below;
+    const size_t slots = p->suspend_below ? 2 * (size_t)capacity : capacity;   // + the finished-resumed region at positions >= capacity
+    for (int b = 0; b < 2; b++) {
+        RT_CUDA(cudaMalloc(&p->v.ray_o[b], sizeof(float4) * slots));
+        RT_CUDA(cudaMalloc(&p->v.ray_d[b], sizeof(float4) * slots));
+        RT_CUDA(cudaMalloc(&p->v.thr[b], sizeof(float4) * slots));
+    }
+    RT_CUDA(cudaMalloc(&p->v.hit, sizeof(uint2) * slots));
+    RT_CUDA(cudaMalloc(&p->v.hit_class, sizeof(uint8_t) * slots));
+    RT_CUDA(cudaMalloc(&p->v.c, sizeof(Counters)));
+    RT_CUDA(cudaHostAlloc(&p->h_live, sizeof(uint32_t) * POLL_SLOTS, cudaHostAllocMapped));
+    RT_CUDA(cudaHostAlloc(&p->h_counters, sizeof(Counters), cudaHostAllocDefault));
+    for (auto& e : p->poll_ev) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    RT_CUDA(cudaEventCreate(&p->ev_begin)); RT_CUDA(cudaEventCreate(&p->ev_end));
+    RT_CUDA(cudaStreamCreateWithFlags(&p->capture_stream, cudaStreamNonBlocking));
+    int sms = 0, occ = 0;
+    RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
+    if (p->suspend_below) {
+        for (int b = 0; b < 2; b++) {
+            RT_CUDA(cudaMalloc(&p->v.cont_walk[b], sizeof(uint4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_o[b], sizeof(float4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_d[b], sizeof(float4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_thr[b], sizeof(float4) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_sp[b], sizeof(uint8_t) * capacity));
+            RT_CUDA(cudaMalloc(&p->v.cont_stack[b], sizeof(int) * (size_t)capacity * RT_SUSPEND_STACK));
+        }
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend_defer<false>, EXTEND_BLOCK, 0));
+        p->grid_extend = sms * std::max(occ, 1);
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_defer, SHADE_BLOCK, 0));
+        p->grid_shade = sms * std::max(occ, 1);
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_block_defer, SHADE_BLOCK, 0));
+        p->grid_shade_block = sms * std::max(occ, 1);
+    } else {
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, SHADE_BLOCK, 0));
+        p->grid_shade = sms * std::max(occ, 1);
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_block, SHADE_BLOCK, 0));
+        p->grid_shade_block = sms * std::max(occ, 1);
+    }
+    return RT_OK;
+}
+
+int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, cudaStream_t stream, rt_render_stats* stats) {
+    if (st.width == 0 || st.height == 0 || st.samples_per_pixel == 0 || st.max_depth == 0 || st.max_depth > 254) {
+        set_error("render: width/height/samples_per_pixel must be > 0 and 1 <= max_depth <= 254");
+        return RT_ERR_INVALID;
+    }
+    const uint32_t s_first = st.sample_first;
+    const uint32_t s_count = st.sample_count ? st.sample_count : st.samples_per_pixel - std::min(st.samples_per_pixel, s_first);
+    if (s_count == 0) { set_error("render: empty sample range (sample_first >= samples_per_pixel)"); return RT_ERR_INVALID; }
+    if ((unsigned long long)s_first + s_count > 0xffffffull) { set_error("render: sample index exceeds 2^24"); return RT_ERR_INVALID; }
+    RT_CUDA(cudaSetDevice(ds.device));
+    const unsigned long long frame_pix = (unsigned long long)st.width * st.height;
+    if (frame_pix >= (1ull << 32)) { set_error("render: more than 2^32 pixels"); return RT_ERR_INVALID; }
+    unsigned long long npix = frame_pix;
+    const uint32_t tile_count = st.tile_count > 1 ? st.tile_count : 1u;
+    if (st.tile_index >= tile_count) { set_error("render: tile_index >= tile_count"); return RT_ERR_INVALID; }
+    if (tile_count > 1) {   // pixels in the film blocks this call owns; only the last block of the frame can be short
+        const unsigned long long nb = (frame_pix + RT_TILE_BLOCK_PIXELS - 1) / RT_TILE_BLOCK_PIXELS;
+        const unsigned long long owned = nb > st.tile_index ? (nb - st.tile_index + tile_count - 1) / tile_count : 0;
+        npix = owned * RT_TILE_BLOCK_PIXELS;
+        if (owned && (owned - 1) * tile_count + st.tile_index == nb - 1) npix -= nb * RT_TILE_BLOCK_PIXELS - frame_pix;
+    }
+    const unsigned long long total = npix * s_count;
+    // pool size: the caller's or 4 Mi paths, never more than the frame has samples, a multiple of 32, at most 2^30
+    uint32_t capacity = (uint32_t)std::min<unsigned long long>(st.pool_paths ? st.pool_paths : (1u << 22), 1ull << 30);
+    capacity = (uint32_t)std::min<unsigned long long>(capacity, std::max<unsigned long long>(total, 32ull));
+    capacity = (capacity + 31u) & ~31u;
+    const uint32_t susp = suspend_threshold(ds, st);
+    if (ds.pool && (ds.pool->v.capacity != capacity || ds.pool->suspend_below != susp)) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
+    if (!ds.pool) {
+        const int rc = pool_create(ds, capacity, susp);
+        if (rc < 0) return rc;
+    }
+    RenderPool& P = *ds.pool;
+    const int variant = extend_variant(ds, st);
+    if (!P.suspend_below && P.extend_variant != variant) {
+        int occ = 0, sms = 0;
+        RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
+        const int rc = extend_occupancy(variant, &occ);
+        if (rc < 0) return rc;
+        P.grid_extend = sms * std::max(occ, 1);
+        P.extend_variant = variant;
+    }
+    const bool count = (st.flags & RT_RENDER_COUNTERS) != 0;
+    const bool timers = (st.flags & RT_RENDER_TIMERS) != 0;
+    const bool block_shade = (st.debug_flags & RT_DEBUG_BLOCK_SHADE) != 0;
+
+    const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
+    const FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, st.debug_flags, total, npix, magic, d_accum, st.tile_index, tile_count};
+    // hard bound: every iteration with live paths retires >= 1 segment of a path of <= max_depth segments (+ 1 for a dead slot)
+    // (deferred extend: a suspended walk advances by at least one leaf phase per iteration, and only whole warps suspend)
+    const uint64_t max_iterations = ((total / capacity + 2) * (uint64_t)(st.max_depth + 1) + POLL_DEPTH + 64) * (P.suspend_below ? 64u : 1u);
+    uint32_t* d_live = nullptr;
+    RT_CUDA(cudaHostGetDevicePointer(&d_live, P.h_live, 0));
+    uint64_t it = 0, launches = 0;
+    size_t n_timer = 0;
+    bool done = total == 0;
+    auto tick = [&]() -> int {   // records the next timer event
+        if (!timers) return RT_OK;
+        if (n_timer == P.timer_ev.size()) { cudaEvent_t e; RT_CUDA(cudaEventCreate(&e)); P.timer_ev.push_back(e); }
+        RT_CUDA(cudaEventRecord(P.timer_ev[n_timer++], stream));
+        return RT_OK;
+    };
+
+    RT_CUDA(cudaEventRecord(P.ev_begin, stream));
+    RT_CUDA(cudaMemsetAsync(P.v.c, 0, sizeof(Counters), stream));
+    if (!done) {   // frame start: the first min(capacity, total) samples fill pool 0
+        const uint32_t n0 = (uint32_t)std::min<unsigned long long>(capacity, total);
+        k_generate<<<(n0 + 255) / 256, 256, 0, stream>>>(ds.view, P.v, fp, n0);
+        launches += 1;
+    }
+    // the three launches of one iteration (cur = parity of the iteration, slot = where turnover publishes the live count)
+    auto launch_iteration = [&](int cur, uint32_t slot, cudaStream_t s, bool timed) -> int {
+        if (timed && tick() < 0) return RT_ERR_CUDA;
+        if (P.suspend_below) {
+            if (count) k_extend_defer<true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
+            else k_extend_defer<false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
+        } else if (count) launch_extend<true>(variant, P.grid_extend, s, ds.view, P.v, fp, cur);
+        else launch_extend<false>(variant, P.grid_extend, s, ds.view, P.v, fp, cur);
+        if (timed && tick() < 0) return RT_ERR_CUDA;
+        if (block_shade) {
+            if (P.suspend_below) k_shade_block_defer<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
+            else k_shade_block<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
+        } else if (P.suspend_below) k_shade_defer<<<P.grid_shade, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
+        else k_shade<<<P.grid_shade, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
+        if (timed && tick() < 0) return RT_ERR_CUDA;
+        k_turnover<<<1, 1, 0, s>>>(P.v, cur, fp.total_samples, d_live + slot);
+        return RT_OK;
+    };
+    // No per-kernel timers: GRAPH_ITERS iterations go to the GPU as ONE CUDA graph.  Small frames and the drain of
+    // every frame are launch-bound (3 launches of a few microseconds per iteration); the graph takes the host out of that
+    // loop.  The graph is captured per call (the frame parameters are kernel arguments) and swapped into the pool's
+    // instantiated graph with cudaGraphExecUpdate — same topology, no re-instantiation.  The host stays one graph ahead of
+    // the live count it reads, so a finished frame costs at most one graph of empty iterations.
+    const bool use_graph = !timers && !done && !(st.debug_flags & RT_DEBUG_NO_GRAPH);
+    if (use_graph) {
+        constexpr int GRAPH_ITERS = POLL_SLOTS;     // a whole period of (parity, live-count slot)
+        cudaGraph_t g = nullptr;
+        RT_CUDA(cudaStreamBeginCapture(P.capture_stream, cudaStreamCaptureModeThreadLocal));
+        int rc = RT_OK;
+        for (int k = 0; k < GRAPH_ITERS && rc == RT_OK; k++) rc = launch_iteration(k & 1, (uint32_t)k, P.capture_stream, false);
+        const cudaError_t ce = cudaStreamEndCapture(P.capture_stream, &g);
+        if (rc < 0 || ce != cudaSuccess || !g) { if (g) cudaGraphDestroy(g); cudaGetLastError(); set_error("render: graph capture failed"); return RT_ERR_CUDA; }
+        if (P.graph_exec) {
+            cudaGraphExecUpdateResultInfo info;
+            if (cudaGraphExecUpdate(P.graph_exec, g, &info) != cudaSuccess) { cudaGetLastError(); cudaGraphExecDestroy(P.graph_exec); P.graph_exec = nullptr; }
+        }
+        if (!P.graph_exec && cuda_fail(cudaGraphInstantiate(&P.graph_exec, g, 0), "cudaGraphInstantiate", __FILE__, __LINE__)) { cudaGraphDestroy(g); return RT_ERR_CUDA; }
+        cudaGraphDestroy(g);
+        for (uint64_t gi = 0; !done; gi++) {
+            RT_CUDA(cudaGraphLaunch(P.graph_exec, stream));
+            RT_CUDA(cudaEventRecord(P.poll_ev[gi & 1], stream));
+            launches += 3 * GRAPH_ITERS; it += GRAPH_ITERS;
+            if (gi >= 1) {   // the graph before this one: its last iteration's live count (a later one is as good: zero stays zero)
+                RT_CUDA(cudaEventSynchronize(P.poll_ev[(gi - 1) & 1]));
+                if (P.h_live[GRAPH_ITERS - 1] == 0) done = true;
+            }
+            if (it > max_iterations + 2 * GRAPH_ITERS) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
+        }
+    }
+    while (!done) {   // direct launches (per-kernel timers, RT_DEBUG_NO_GRAPH), polled POLL_DEPTH iterations behind
+        const int rc = launch_iteration((int)(it & 1), (uint32_t)(it % POLL_SLOTS), stream, true);
+        if (rc < 0) return rc;
+        RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
+        launches += 3;
+        if (it >= POLL_DEPTH) {
+            const uint64_t old = it - POLL_DEPTH;
+            RT_CUDA(cudaEventSynchronize(P.poll_ev[old % POLL_SLOTS]));
+            if (P.h_live[old % POLL_SLOTS] == 0) done = true;
+        }
+        if (it > max_iterations) { set_error("render: wavefront did not drain (internal error)"); return RT_ERR_STATE; }
+        it++;
+    }
+    if (tick() < 0) return RT_ERR_CUDA;
+    RT_CUDA(cudaMemcpyAsync(P.h_counters, P.v.c, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+    RT_CUDA(cudaEventRecord(P.ev_end, stream));
+    RT_CUDA(cudaStreamSynchronize(stream));
+    RT_CUDA(cudaGetLastError());
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        const Counters& c = *P.h_counters;
+        stats->samples = std::min<unsigned long long>(c.next_sample, total);
+        stats->rays = c.total_rays;
+        stats->iterations = it;
+        stats->kernel_launches = launches;
+        stats->nodes_visited = c.nodes;
+        stats->prim_tests = c.prim_tests;
+        stats->node_slots = c.node_slots;
+        if (timers) {   // per-kernel device time, summed over the iterations of this frame: 3 events per iteration + 1
+            double ext = 0, shd = 0, fin = 0;
+            const std::vector<cudaEvent_t>& ev = P.timer_ev;
+            for (size_t k = 0; k + 3 < n_timer; k += 3) {
+                float a = 0, b = 0, d = 0;
+                cudaEventElapsedTime(&a, ev[k], ev[k + 1]);
+                cudaEventElapsedTime(&b, ev[k + 1], ev[k + 2]);
+                cudaEventElapsedTime(&d, ev[k + 2], ev[k + 3]);
+                ext += a; shd += b; fin += d;
+            }
+            if (n_timer) cudaEventElapsedTime(&stats->ms_generate, P.ev_begin, ev[0]);
+            stats->ms_extend = (float)ext; stats->ms_shade = (float)shd; stats->ms_finish = (float)fin;
+        }
+        cudaEventElapsedTime(&stats->ms_total, P.ev_begin, P.ev_end);
+    }
+    return RT_OK;
+}
+
+} // namespace
+} // namespace rtb
+
+using namespace rtb;
+
+extern "C" int rt_render_device(rt_scene* s, const rt_render_settings* st, float* d_accum, void* cuda_stream, rt_render_stats* stats) {
+    if (!s || !st || !d_accum) { set_error("render: bad argument"); return RT_ERR_INVALID; }
+    DeviceScene* ds = nullptr;
+    const int rc = device_scene_current(s, &ds, "render");
+    if (rc < 0) return rc;
+    return render_impl(*ds, *st, d_accum, (cudaStream_t)cuda_stream, stats);
+}
+
+extern "C" int rt_render(rt_scene* s, const rt_render_settings* st, float* out_rgb, rt_render_stats* stats) {
+    if (!s || !st || !out_rgb) { set_error("render: bad argument"); return RT_ERR_INVALID; }
+    DeviceScene* ds = nullptr;
+    int rc = device_scene_current(s, &ds, "render");
+    if (rc < 0) return rc;
+    RT_CUDA(cudaSetDevice(ds->device));
+    const size_t n = (size_t)st->width * st->height * 3;
+    if (n == 0) { set_error("render: empty frame"); return RT_ERR_INVALID; }
+    // the accumulation buffer lives with the scene (grow-only): no allocation per call, nothing to leak on an error path
+    RT_CUDA(ds->accum.reserve(sizeof(float) * n));
+    float* d_accum = (float*)ds->accum.p;
+    cudaStream_t stream = ds->stream;
+    const bool accumulate = (st->flags & RT_RENDER_ACCUMULATE) != 0;   // progressive: out_rgb carries the sums so far
+    if (accumulate) RT_CUDA(cudaMemcpyAsync(d_accum, out_rgb, sizeof(float) * n, cudaMemcpyHostToDevice, stream));
+    else RT_CUDA(cudaMemsetAsync(d_accum, 0, sizeof(float) * n, stream));
+    rc = render_impl(*ds, *st, d_accum, stream, stats);
+    if (rc < 0) return rc;
+    if (!accumulate) {
+        const uint32_t s_count = st->sample_count ? st->sample_count : st->samples_per_pixel - std::min(st->samples_per_pixel, st->sample_first);
+        k_scale<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(d_accum, d_accum, n, 1 / (float)s_count);
+    }
+    RT_CUDA(cudaMemcpyAsync(out_rgb, d_accum, sizeof(float) * n, cudaMemcpyDeviceToHost, stream));
+    RT_CUDA(cudaStreamSynchronize(stream));
+    return RT_OK;
+}
+
+// Measured FP32 peak of `device` ("measure with an FMA microbenchmark on the box"): a grid of independent FMA
+// chains, CUDA events, best of 5.  2 flop per FMA per lane.
+extern "C" int rt_measure_fp32_peak(int device, double* tflops) {
+    if (!tflops) { set_error("fp32_peak: null out pointer"); return RT_ERR_INVALID; }
+    RT_CUDA(cudaSetDevice(device));
+    int sms = 0;
+    RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const int blocks = sms * 8, threads = 256, iters = 4096;
+    float* d = nullptr;
+    RT_CUDA(cudaMalloc(&d, sizeof(float) * blocks * threads));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    double best = 0;
+    for (int rep = 0; rep < 6; rep++) {
+        cudaEventRecord(e0);
+        k_fma_peak<<<blocks, threads>>>(d, 1.0000001f, 1e-7f, iters);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double tf = 2.0 * 8 * 16 * (double)iters * blocks * threads / (ms * 1e-3) / 1e12;
+        if (rep && tf > best) best = tf;      // the first launch warms the clocks up
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    const cudaError_t err = cudaGetLastError();
+    cudaFree(d);
+    if (cuda_fail(err, "k_fma_peak", __FILE__, __LINE__)) return RT_ERR_CUDA;
+    *tflops = best;
+    return RT_OK;
+}
