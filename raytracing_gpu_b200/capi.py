@@ -20,7 +20,8 @@ class RenderSettings(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("samples_per_pixel", C.c_uint32),
                 ("max_depth", C.c_uint32), ("seed", C.c_uint32), ("sample_first", C.c_uint32),
                 ("sample_count", C.c_uint32), ("flags", C.c_uint32), ("pool_paths", C.c_uint32),
-                ("tile_index", C.c_uint32), ("tile_count", C.c_uint32), ("reserved", C.c_uint32 * 5)]
+                ("tile_index", C.c_uint32), ("tile_count", C.c_uint32), ("extend_defer", C.c_uint32), ("traversal", C.c_uint32),
+                ("debug_flags", C.c_uint32), ("reserved", C.c_uint32 * 2)]
 
 
 class RenderStats(C.Structure):
@@ -36,7 +37,22 @@ class BuildStats(C.Structure):
                 ("ms_sort", C.c_float), ("ms_hierarchy", C.c_float), ("ms_refit", C.c_float),
                 ("ms_collapse", C.c_float), ("ms_total", C.c_float), ("bvh_depth", C.c_uint32), ("build_rounds", C.c_uint32),
                 ("sah_internal", C.c_float), ("ploc_radius", C.c_uint32), ("builder", C.c_uint32),
-                ("reserved", C.c_uint32 * 3)]
+                ("n_wide_nodes", C.c_uint32), ("ms_host", C.c_float), ("reserved", C.c_uint32 * 1)]
+
+
+class BuildSettings(C.Structure):
+    _fields_ = [("builder", C.c_uint32), ("sah_max_prims", C.c_uint32), ("ploc_radius", C.c_uint32), ("ploc_top", C.c_uint32),
+                ("wide_nodes", C.c_uint32), ("flags", C.c_uint32), ("reserved", C.c_uint32 * 10)]
+
+
+BUILD_AUTO, BUILD_KARRAS, BUILD_PLOC, BUILD_HOST_SAH, BUILD_GPU_SAH = 0, 1, 2, 3, 4
+BUILDERS = {"auto": 0, "karras": 1, "ploc": 2, "host_sah": 3, "sah": 4, "gpu_sah": 4}
+BUILDER_KARRAS, BUILDER_PLOC, BUILDER_HOST_SAH, BUILDER_GPU_SAH = 0, 1, 2, 3      # rt_build_stats.builder
+WIDE_AUTO, WIDE_OFF, WIDE_ON = 0, 1, 2
+BUILD_TRACE = 1
+DEFER_AUTO, DEFER_OFF = 0, 1
+TRAVERSAL_FORCE = 0x100
+DEBUG_NO_GRAPH, DEBUG_RASTER_FILM, DEBUG_BLOCK_SHADE = 1, 2, 4
 
 
 class CatalogParams(C.Structure):
@@ -101,6 +117,8 @@ def lib():
         "rt_scene_replay": (i32, [vp, vp, C.c_size_t]), "rt_scene_flatten": (i32, [vp]),
         "rt_scene_export_size": (C.c_size_t, [vp]), "rt_scene_export": (i32, [vp, vp, C.c_size_t]),
         "rt_image_height": (i32, [i32, f32]), "rt_scene_commit": (i32, [vp, i32, C.POINTER(BuildStats)]),
+        "rt_scene_commit_ex": (i32, [vp, i32, C.POINTER(BuildSettings), C.POINTER(BuildStats)]),
+        "rt_measure_fp32_peak": (i32, [i32, C.POINTER(C.c_double)]), "rt_scene_bvh_nodes": (i32, [vp, vp, C.c_size_t]),
         "rt_first_hit": (i32, [vp, vp, i32, f32, vp, vp, vp]),
         "rt_render": (i32, [vp, C.POINTER(RenderSettings), vp, C.POINTER(RenderStats)]),
         "rt_render_device": (i32, [vp, C.POINTER(RenderSettings), vp, vp, C.POINTER(RenderStats)]),
@@ -138,6 +156,13 @@ def image_height(width, aspect):
 
 
 image_height_of = image_height
+
+
+def measure_fp32_peak(device=0):
+    """TFLOP/s of an FMA microbenchmark on `device` (rt_measure_fp32_peak)."""
+    v = C.c_double()
+    _check(lib().rt_measure_fp32_peak(int(device), C.byref(v)))
+    return v.value
 
 
 def quantize_frame(rgb):
@@ -294,10 +319,25 @@ class Scene:
         _check(lib().rt_scene_export(self._h, buf.ctypes.data, n))
         return buf
 
-    def commit(self, device=0):
+    def commit(self, device=0, builder="auto", sah_max_prims=0, ploc_radius=0, ploc_top=0, wide_nodes=WIDE_AUTO, trace=False):
+        """rt_scene_commit_ex.  builder: "auto" | "sah" (GPU sweep) | "host_sah" | "ploc" | "karras"."""
+        bs = BuildSettings(builder=BUILDERS[builder] if isinstance(builder, str) else int(builder), sah_max_prims=sah_max_prims,
+                           ploc_radius=ploc_radius, ploc_top=ploc_top, wide_nodes=wide_nodes, flags=BUILD_TRACE if trace else 0)
         st = BuildStats()
-        _check(lib().rt_scene_commit(self._h, int(device), C.byref(st)))
+        _check(lib().rt_scene_commit_ex(self._h, int(device), C.byref(bs), C.byref(st)))
         return st
+
+    def bvh_nodes(self):
+        """The committed scene's binary BVH: (n_nodes, 16) uint32 words (include/rt_b200.h rt_scene_bvh_nodes)."""
+        cap = 1 << 16
+        while True:
+            buf = np.zeros((cap, 16), np.uint32)
+            rc = lib().rt_scene_bvh_nodes(self._h, buf.ctypes.data, buf.nbytes)
+            if rc >= 0:
+                return buf[:rc].copy()
+            if "too small" not in lib().rt_last_error().decode() or cap > (1 << 26):
+                _check(rc)
+            cap *= 8
 
     def first_hit(self, rays, t_min=0.001, xi=None):
         rays = _f32(rays).reshape(-1, 7)
@@ -310,10 +350,11 @@ class Scene:
         return ids, t
 
     def render(self, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0, flags=0, pool_paths=0,
-               tile_index=0, tile_count=0):
+               tile_index=0, tile_count=0, extend_defer=0, traversal=0, debug_flags=0):
         st = RenderSettings(width=width, height=height, samples_per_pixel=spp, max_depth=max_depth, seed=seed,
                             sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths,
-                            tile_index=tile_index, tile_count=tile_count)
+                            tile_index=tile_index, tile_count=tile_count, extend_defer=extend_defer, traversal=traversal,
+                            debug_flags=debug_flags)
         out = np.empty((height, width, 3), np.float32)
         stats = RenderStats()
         _check(lib().rt_render(self._h, C.byref(st), out.ctypes.data, C.byref(stats)))
@@ -348,11 +389,12 @@ class Scene:
         return out, stats
 
     def render_device(self, d_accum_ptr, width, height, spp, max_depth=50, seed=1984, sample_first=0, sample_count=0,
-                      flags=0, pool_paths=0, stream=None, tile_index=0, tile_count=0):
+                      flags=0, pool_paths=0, stream=None, tile_index=0, tile_count=0, extend_defer=0, traversal=0, debug_flags=0):
         """Accumulate sums into a caller-owned device buffer (e.g. a torch CUDA tensor's data_ptr())."""
         st = RenderSettings(width=width, height=height, samples_per_pixel=spp, max_depth=max_depth, seed=seed,
                             sample_first=sample_first, sample_count=sample_count, flags=flags, pool_paths=pool_paths,
-                            tile_index=tile_index, tile_count=tile_count)
+                            tile_index=tile_index, tile_count=tile_count, extend_defer=extend_defer, traversal=traversal,
+                            debug_flags=debug_flags)
         stats = RenderStats()
         _check(lib().rt_render_device(self._h, C.byref(st), C.c_void_p(d_accum_ptr), C.c_void_p(stream or 0), C.byref(stats)))
         return stats

@@ -2,12 +2,15 @@
 import ctypes as C
 import os
 import subprocess
+import sys
 
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 ORACLE_DIR = os.path.join(ROOT, "oracle")
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
 
 NAMED_SCENES = ["basic", "first", "big1", "two_spheres", "two_perlin", "cornell", "cornell_smoke", "triangle", "triangles"]
 
@@ -178,39 +181,7 @@ def rmse(a, b):
     return float(np.sqrt(np.mean((a - b) ** 2)))
 
 
-def procedural_image(w, h, seed=7):
-    """Synthetic RGB8 texture standing in for earthmap.jpg / mesh textures (reference assets are not copied)."""
-    rng = np.random.default_rng(seed)
-    y, x = np.mgrid[0:h, 0:w].astype(np.float32)
-    img = np.stack([127 + 120 * np.sin(x * 0.021) * np.cos(y * 0.017), 127 + 120 * np.sin(x * 0.013 + y * 0.011),
-                    127 + 120 * np.cos(x * 0.007 - y * 0.019)], axis=-1)
-    img += rng.integers(-6, 7, size=img.shape)
-    return np.clip(img, 0, 255).astype(np.uint8)
-
-
-def procedural_mesh(n_theta, n_phi, seed=3):
-    """Seeded bumpy sphere mesh (stands in for the missing cup/backpack .obj): flat arrays as create_meshes_d
-    takes them (vertices 3V, indices 3T, uvs 2V, normals 3V — normals deliberately not unit length)."""
-    rng = np.random.default_rng(seed)
-    th = np.linspace(0.05, np.pi - 0.05, n_theta, dtype=np.float64)
-    ph = np.linspace(0, 2 * np.pi, n_phi, endpoint=False, dtype=np.float64)
-    T, P = np.meshgrid(th, ph, indexing="ij")
-    r = 0.5 + 0.05 * np.sin(5 * T) * np.cos(4 * P) + 0.01 * rng.random(T.shape)
-    x, y, z = r * np.sin(T) * np.cos(P), r * np.cos(T) + 0.6, r * np.sin(T) * np.sin(P)
-    verts = np.stack([x, y, z], -1).reshape(-1, 3).astype(np.float32)
-    norms = (np.stack([np.sin(T) * np.cos(P), np.cos(T), np.sin(T) * np.sin(P)], -1).reshape(-1, 3) *
-             (0.5 + rng.random((n_theta * n_phi, 1)))).astype(np.float32)
-    uvs = np.stack([P / (2 * np.pi), 1 - T / np.pi], -1).reshape(-1, 2).astype(np.float32)
-    idx = []
-    for i in range(n_theta - 1):
-        for j in range(n_phi):
-            a, b = i * n_phi + j, i * n_phi + (j + 1) % n_phi
-            c, d = a + n_phi, b + n_phi
-            idx += [a, c, b, b, c, d]
-    return verts, np.asarray(idx, np.uint32), uvs, norms
-
-
-MESH_CAMERA = np.asarray([0, 1.2, -3, 0, 0.6, 0, 0, 1, 0, 30, 16.0 / 9.0, 0.0, 10.0, 0, 1], np.float32)
+from workloads import procedural_image, procedural_mesh, MESH_CAMERA  # noqa: E402,F401  (synthetic inputs shared with bench.py)
 
 
 def media_leaf_ids(blob):
