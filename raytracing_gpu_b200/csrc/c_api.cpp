@@ -283,6 +283,7 @@ int rt_set_camera_raw(rt_scene* s, const rt_flat_camera* cam) {
 /* ---- flatten / export ---- */
 int rt_scene_flatten(rt_scene* s) {
     CHECK_SCENE(s);
+    if (s->host.flat.valid) return (int)s->host.flat.hdr.num_leaf_ids;   // unchanged since the last flattening (a committed device copy stays current)
     std::string e;
     const int r = s->host.flatten(e);
     if (r < 0) g_err = e;
