@@ -182,16 +182,27 @@ def reference_cuda(workload, budget_s=20.0):
             "nan_pixels": res["nan_pixels"], "image_mean": res["image_mean"]}
 
 
+def config_of(workload, world, width, height, spp, partition):
+    """The config dict both arms print (the driver compares them key by key)."""
+    return {"workload": WORKLOADS[workload][4], "width": width, "height": height, "spp_per_gpu": spp, "spp_total": spp * world,
+            "max_depth": 50, "partition": f"{partition}-split x{world} + one NCCL reduce" if world > 1 else "single GPU"}
+
+
 def print_reference_line(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     scene_name, width, aspect, spp, desc = WORKLOADS[args.workload]
+    width = args.width or width
+    spp = args.spp or spp
+    world = max(1, args.gpus)
     cb, ms = reference_cpu(args.workload, args.steps, args.warmup, budget_s=60.0)
+    cfg = config_of(args.workload, world, width, image_height(width, aspect), spp, args.partition)
+    note = (f"reference's own render()/color_f() compiled for the host (oracle/_ref), CPU only; each step renders "
+            f"{cb['spp_timed']} of the spp_per_gpu samples of the full frame (cpu_baseline.sample)")
     line = {"impl": "reference", "metric": "Msamples/s", "value": cb["value"], "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "note": "reference's own render()/color_f() compiled for the host (oracle/_ref); CPU only"},
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "note": note, "spp_timed": cb["spp_timed"],
             "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -199,6 +210,99 @@ def print_reference_line(args):
 # --------------------------------------------------------------------------------------------------------------
 # product arm
 # --------------------------------------------------------------------------------------------------------------
+class Frame:
+    """One workload on this rank's GPU: committed scene, device accumulation buffer, pinned host image."""
+
+    def __init__(self, rt, torch, dist, workload, local, rank, world, partition, pool, width=0, spp=0, strong=False):
+        scene_name, w, aspect, s, self.desc = WORKLOADS[workload]
+        self.rt, self.torch, self.dist = rt, torch, dist
+        self.workload, self.scene_name, self.local, self.rank, self.world, self.partition, self.pool = workload, scene_name, local, rank, world, partition, pool
+        self.width = width or w
+        self.spp = spp or s                                   # per GPU (weak) or total (strong)
+        self.total_spp = self.spp if strong else self.spp * world
+        self.height = image_height(self.width, aspect)
+        self.npix = self.width * self.height
+        self.dev = torch.device("cuda", local)
+        self.sc, _ = build_scene(rt, scene_name, aspect)
+        self.build = self.sc.commit(local)
+        self.blob_bytes = int(len(self.sc.export()))
+        self.image_bytes = {"final": 3410 * 1518 * 4, "mesh": 2048 * 2048 * 4}.get(scene_name, 0)     # RGBA8 as uploaded
+        self.stream = torch.cuda.current_stream().cuda_stream
+        self.accum = torch.zeros(self.height, self.width, 3, device=self.dev, dtype=torch.float32)
+        self.out = torch.empty_like(self.accum)
+        self.host_img = torch.empty(self.height, self.width, 3, dtype=torch.float32).pin_memory()
+        self.reduce_ms = []
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def step(self, flags=0, time_reduce=False, **kw):
+        torch, dist = self.torch, self.dist
+        self.accum.zero_()
+        if self.partition == "tile":
+            first, count, ti, tc = 0, self.total_spp, self.rank, self.world
+        else:
+            base, rem = divmod(self.total_spp, self.world)
+            count, first, ti, tc = base + (1 if self.rank < rem else 0), self.rank * base + min(self.rank, rem), 0, 1
+        st = self.sc.render_device(self.accum.data_ptr(), self.width, self.height, self.total_spp, max_depth=50, seed=SEED, sample_first=first,
+                                   sample_count=count, flags=flags, pool_paths=self.pool, stream=self.stream, tile_index=ti, tile_count=tc, **kw)
+        if self.world > 1:
+            if time_reduce:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                dist.reduce(self.accum, dst=0, op=dist.ReduceOp.SUM)
+                e1.record()
+                e1.synchronize()
+                self.reduce_ms.append(e0.elapsed_time(e1))
+            else:
+                dist.reduce(self.accum, dst=0, op=dist.ReduceOp.SUM)
+        torch.mul(self.accum, 1.0 / self.total_spp, out=self.out)
+        return st
+
+    def e2e_step(self):
+        self.sc.commit(self.local)
+        self.step()
+        if self.rank == 0:
+            self.host_img.copy_(self.out, non_blocking=True)
+
+    def timed(self, fn, k):
+        torch, dist = self.torch, self.dist
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res = [fn() for _ in range(k)]
+        e1.record()
+        self.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), res
+
+    def msamples(self, ms_step):
+        return self.npix * self.total_spp / (ms_step * 1e-3) / 1e6
+
+
+def short_record(fr, steps, warmup):
+    """value / e2e / kernel ms of one workload (used for the per-scene `workloads` block)."""
+    for _ in range(warmup):
+        fr.step()
+    ms, stats = fr.timed(fr.step, steps)
+    ms_step = ms / steps
+    _, ts = fr.timed(lambda: fr.step(flags=2), 1)
+    fr.e2e_step()
+    ms_e2e, _ = fr.timed(fr.e2e_step, steps)
+    rays = float(np.mean([s.rays for s in stats]))
+    t = ts[0]
+    return {"workload": fr.desc, "width": fr.width, "height": fr.height, "spp": fr.total_spp, "steps": steps, "value": fr.msamples(ms_step),
+            "unit": "Msamples/s", "ms_per_step": ms_step, "mrays_per_s": rays / (ms_step * 1e-3) / 1e6,
+            "e2e": fr.msamples(ms_e2e / steps), "prims": int(fr.build.n_prims), "bvh_builder": int(fr.build.builder),
+            "bvh_build_ms": float(fr.build.ms_total), "commit_host_ms": float(fr.build.ms_host),
+            "kernel_ms_per_step": {"extend": t.ms_extend, "shade": t.ms_shade, "generate": t.ms_generate, "turnover": t.ms_finish,
+                                   "note": "per-kernel CUDA events of a separate pass with direct launches (no CUDA graph)"}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -213,6 +317,7 @@ def main():
                     help="multi-GPU split: sample ranges (default) or interleaved film blocks; one NCCL reduce either way")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the per-scene `workloads` block and the config-5 `strong` record")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -222,7 +327,6 @@ def main():
     import torch
     import torch.distributed as dist
     import raytracing_gpu_b200 as rt
-    from raytracing_gpu_b200.parallel import sample_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -233,79 +337,32 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    dev = torch.device("cuda", local)
 
-    scene_name, width, aspect, spp, desc = WORKLOADS[args.workload]
-    width = args.width or width
-    spp = args.spp or spp
-    height = rt.image_height(width, np.float32(aspect))
-    total_spp = spp * world
-    npix = width * height
-
-    sc, _ = build_scene(rt, scene_name, aspect)
-    build = sc.commit(local)
-    blob_bytes = int(len(sc.export()))
-    stream = torch.cuda.current_stream().cuda_stream
-    accum = torch.zeros(height, width, 3, device=dev, dtype=torch.float32)
-    out = torch.empty_like(accum)
-    host_img = torch.empty(height, width, 3, dtype=torch.float32).pin_memory()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def step(flags=0):
-        accum.zero_()
-        if args.partition == "tile":
-            first, count, ti, tc = 0, total_spp, rank, world
-        else:
-            (first, count), ti, tc = sample_range(total_spp, world, rank), 0, 1
-        st = sc.render_device(accum.data_ptr(), width, height, total_spp, max_depth=50, seed=SEED, sample_first=first,
-                              sample_count=count, flags=flags, pool_paths=args.pool, stream=stream, tile_index=ti, tile_count=tc)
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
-        torch.mul(accum, 1.0 / total_spp, out=out)
-        return st
-
-    def timed(fn, k):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        res = [fn() for _ in range(k)]
-        e1.record()
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), res
-
+    fr = Frame(rt, torch, dist, args.workload, local, rank, world, args.partition, args.pool, width=args.width, spp=args.spp)
+    build = fr.build
     for _ in range(args.warmup):
-        step()
+        fr.step()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ms_total, stats = timed(step, args.steps)
+    ms_total, stats = fr.timed(fr.step, args.steps)
     clk = clocks.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
-    value = npix * total_spp / (ms_step * 1e-3) / 1e6
-    rays = torch.tensor([float(np.mean([s.rays for s in stats]))], device=dev, dtype=torch.float64)
+    value = fr.msamples(ms_step)
+    rays = torch.tensor([float(np.mean([s.rays for s in stats]))], device=fr.dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(rays)
     rays_per_step = float(rays.item())
     launches = int(sum(s.kernel_launches for s in stats)) + 2 * args.steps      # + zero + scale kernels per step
 
-    # dominant kernel (extend): separate pass with per-kernel CUDA events (not part of the timed region above)
-    _, tstats = timed(lambda: step(flags=2), 1)
+    # dominant kernel (extend): separate pass with per-kernel CUDA events and direct launches (not part of the timed region above)
+    _, tstats = fr.timed(lambda: fr.step(flags=2), 1)
     ts = tstats[0]
     ext_launches = int(ts.iterations)
     ext_ms = ts.ms_extend / max(ext_launches, 1)
     ext_bytes = 48.0 * ts.rays / max(ext_launches, 1)                 # ray 32 B in + hit 16 B out per segment
     peaks, peak_src = measured_peaks()
-    # scenes of 65 536 primitives and more walk through the deferred extend (wavefront.cu: SUSPEND_MIN_PRIMS; RT_SUSPEND overrides)
-    forced = os.environ.get("RT_SUSPEND")
-    deferred = (int(forced) > 0) if forced not in (None, "") else int(build.n_prims) >= 65536
-    extend_kernel = "k_extend_defer" if deferred else "k_extend"
+    extend_kernel = "k_extend_defer" if int(build.n_prims) >= 65536 else "k_extend"   # wavefront.cu: SUSPEND_MIN_PRIMS
     achieved = ext_bytes / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -314,32 +371,59 @@ def main():
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "traffic": traffic, "kernel": extend_kernel, "peak_source": peak_src, "launches_per_step": ext_launches,
                 "avg_launch_ms": ext_ms, "share_of_step": ts.ms_extend / max(ts.ms_total, 1e-9),
-                "kernel_ms_per_step": {"extend": ts.ms_extend, "shade": ts.ms_shade, "generate": ts.ms_generate, "turnover": ts.ms_finish}}
-    # FP32 roofline (the binding one): algorithmic flops from measured traversal counters (SURVEY §8d figures)
-    _, cstats = timed(lambda: step(flags=1), 1)
+                "kernel_ms_per_step": {"extend": ts.ms_extend, "shade": ts.ms_shade, "generate": ts.ms_generate, "turnover": ts.ms_finish,
+                                       "total_of_this_pass": ts.ms_total,
+                                       "note": "separate pass with direct launches and 3 events per iteration: sums exceed ms_per_step, "
+                                               "which is timed with 8 iterations per CUDA graph"}}
+    # FP32 roofline (the binding one): algorithmic flops from measured traversal counters (SURVEY §8d figures) against the FMA
+    # microbenchmark run on THIS GPU
+    _, cstats = fr.timed(lambda: fr.step(flags=1), 1)
     cs = cstats[0]
     flops = 24.0 * 2 * cs.nodes_visited + 45.0 * cs.prim_tests + 55.0 * cs.rays
-    fp32_peak = 148 * 128 * 2 * (peaks.get("sm_max_mhz", 1965.0) * 1e6) / 1e12
+    fp32_nominal = 148 * 128 * 2 * (peaks.get("sm_max_mhz", 1965.0) * 1e6) / 1e12
+    try:
+        fp32_peak, fp32_src = rt.capi.measure_fp32_peak(local), "measured: FMA microbenchmark on this GPU (rt_measure_fp32_peak), best of 5"
+    except Exception as e:                                            # never lose the bench line over the probe
+        fp32_peak, fp32_src = fp32_nominal, f"nominal (probe failed: {e})"
     roofline_fp32 = {"bound": "fp32", "achieved": flops / (ms_step * 1e-3) / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
-                     "frac": flops / (ms_step * 1e-3) / 1e12 / fp32_peak, "peak_source": "nominal 148 SM x 128 lanes x 2 x max SM clock",
+                     "frac": flops / (ms_step * 1e-3) / 1e12 / fp32_peak, "peak_source": fp32_src, "peak_nominal": fp32_nominal,
                      "nodes_per_ray": cs.nodes_visited / max(cs.rays, 1), "prim_tests_per_ray": cs.prim_tests / max(cs.rays, 1),
                      "rays_per_sample": cs.rays / max(cs.samples, 1),
                      "warp_lane_utilisation_node_loop": cs.nodes_visited / max(cs.node_slots, 1)}
 
-    # end to end through the C-ABI with host buffers: commit (H2D + LBVH build) + render + reduce + D2H
+    # end to end through the C-ABI with host buffers: commit (H2D + BVH build) + render + reduce + D2H
     e2e = None
     if not args.no_e2e:
-        def e2e_step():
-            sc.commit(local)
-            step()
-            if rank == 0:
-                host_img.copy_(out, non_blocking=True)
-        e2e_step()
-        ms_e2e, _ = timed(e2e_step, args.steps)
-        image_bytes = sum(int(w) * int(h) * 4 for w, h in [(3410, 1518)]) if scene_name == "final" else 0
-        e2e = {"value": npix * total_spp / (ms_e2e / args.steps * 1e-3) / 1e6, "unit": "Msamples/s",
-               "h2d_bytes_per_step": blob_bytes + image_bytes, "d2h_bytes_per_step": npix * 12,
-               "includes": "rt_scene_commit (scene H2D + GPU LBVH build) + render + reduce + image D2H"}
+        fr.e2e_step()
+        ms_e2e, _ = fr.timed(fr.e2e_step, args.steps)
+        b2 = fr.sc.commit(local)
+        e2e = {"value": fr.msamples(ms_e2e / args.steps), "unit": "Msamples/s",
+               "h2d_bytes_per_step": fr.blob_bytes + fr.image_bytes, "d2h_bytes_per_step": fr.npix * 12,
+               "includes": "rt_scene_commit (scene tables + image texture H2D from pinned staging, BVH build on the GPU) + render + reduce + image D2H",
+               "commit_host_ms": float(b2.ms_host), "commit_gpu_ms": float(b2.ms_total), "bvh_builder": int(b2.builder)}
+
+    # per-scene block (the metric is per scene) and BASELINE config 5 (strong scaling)
+    extras, strong = None, None
+    if not args.no_extras and args.workload == "final":
+        if world == 1:
+            extras = {}
+            for name in ("big1", "cornell_smoke", "mesh"):
+                f2 = Frame(rt, torch, dist, name, local, rank, world, args.partition, args.pool)
+                extras[name] = short_record(f2, 2, 3)
+                del f2
+                torch.cuda.empty_cache()
+        f5 = Frame(rt, torch, dist, "final_c5", local, rank, world, "sample", args.pool, strong=True)
+        f5.sc.render_device(f5.accum.data_ptr(), f5.width, f5.height, 8, max_depth=50, seed=SEED, stream=f5.stream)   # warm-up: pools, graph
+        ms5, st5 = f5.timed(lambda: f5.step(time_reduce=True), 1)
+        rays5 = torch.tensor([float(st5[0].rays)], device=f5.dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(rays5)
+        strong = {"workload": f5.desc, "width": f5.width, "height": f5.height, "spp_total": f5.total_spp, "n_gpus": world, "steps": 1,
+                  "scaling": "strong", "value": f5.msamples(ms5), "unit": "Msamples/s", "ms_per_step": ms5,
+                  "mrays_per_s": float(rays5.item()) / (ms5 * 1e-3) / 1e6, "reduce_ms": (f5.reduce_ms[-1] if f5.reduce_ms else 0.0),
+                  "render_ms_this_rank": float(st5[0].ms_total), "accum_bytes": f5.npix * 12,
+                  "partition": f"sample-split x{world} + one NCCL reduce" if world > 1 else "single GPU"}
+        del f5
 
     cb = rc = None
     if rank == 0 and not args.no_cpu_baseline:
@@ -348,19 +432,22 @@ def main():
             rc = reference_cuda(args.workload)
 
     if rank == 0:
+        cfg = config_of(args.workload, world, fr.width, fr.height, fr.spp, args.partition)
+        extra_cfg = {"l2": "working set (pool + queues) > L2; accumulation buffer re-zeroed each step",
+                     "prims": int(build.n_prims), "bvh_nodes": int(build.n_nodes), "bvh_build_ms": float(build.ms_total),
+                     "bvh_builder": {0: "karras (GPU)", 1: "PLOC (GPU) + SAH-swept top (GPU)", 2: "host SAH sweep", 3: "SAH sweep (GPU)"}[int(build.builder)]}
+        ncu = NCU_EVIDENCE.get(args.workload)
+        if ncu and ncu.get("captured_at") != rt.lib().rt_version().decode():
+            ncu = None
         line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32", "data": "synthetic",
-                "config": {"workload": desc, "width": width, "height": height, "spp_per_gpu": spp, "spp_total": total_spp,
-                           "max_depth": 50, "partition": f"{args.partition}-split x{world} + one NCCL reduce" if world > 1 else "single GPU",
-                           "l2": "working set (pool + queues) > L2; accumulation buffer re-zeroed each step",
-                           "prims": int(build.n_prims), "bvh_nodes": int(build.n_nodes), "bvh_build_ms": float(build.ms_total)},
-                "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays_per_step / (npix * total_spp),
+                "dtype": "f32", "data": "synthetic", "config": cfg, "scene": extra_cfg,
+                "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6, "rays_per_sample": rays_per_step / (fr.npix * fr.total_spp),
                 "gpu_launches": launches, "clocks": clk, "roofline": roofline, "roofline_fp32": roofline_fp32,
-                # what actually bounds the dominant kernel: unit utilisation from the committed ncu capture of this workload
-                # (a profiler reading, recorded once per version — not measured by this run)
-                "ncu_evidence": NCU_EVIDENCE.get(args.workload), "e2e": e2e,
-                "cpu_baseline": cb, "reference_cuda": rc}
+                "ncu_evidence": ncu, "e2e": e2e, "workloads": extras, "strong": strong,
+                "cpu_baseline": cb, "reference_cuda": rc,
+                "vs_reference_cuda": (value / rc["value"] if rc and rc.get("value") else None),
+                "library": rt.lib().rt_version().decode()}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
