@@ -1081,6 +1081,20 @@ int build_bvh(DeviceScene& ds, const rt_build_settings& bs, const DPrim* d_prims
     RT_CUDA(cudaEventRecord(ev[2], stream));
     ds.build.build_rounds = 0; ds.build.ploc_radius = 0; ds.build.bvh_depth = 0; ds.build.sah_internal = 0.f;
 
+    // Morton-prefix hierarchy: the A/B builder, and the last resort for inputs the SAH-driven builders make chains of
+    // (thousands of identical boxes): equal keys split by index bits, so its depth is bounded by key + index bits
+    auto build_karras = [&]() -> int {
+        ds.build.builder = RT_BUILDER_KARRAS;
+        ds.build.bvh_depth = 0; ds.build.sah_internal = 0.f; ds.build.build_rounds = 0; ds.build.ploc_radius = 0;
+        RT_CUDA(cudaMemsetAsync(visit, 0, sizeof(uint32_t) * n, stream));
+        if (n > 1) k_karras<<<gb, tb, 0, stream>>>(kin, (int)n, left, right, parent_internal, parent_leaf);
+        RT_CUDA(cudaEventRecord(ev[3], stream));
+        k_refit<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, right, parent_internal, parent_leaf, leaf_lo, leaf_hi, node_lo, node_hi, visit);
+        RT_CUDA(cudaEventRecord(ev[4], stream));
+        k_emit_nodes<<<gb, tb, 0, stream>>>((int)n, left, right, leaf_lo, leaf_hi, node_lo, node_hi, nodes);
+        return RT_OK;
+    };
+
     bool built = false;
     if (choice == RT_BUILD_GPU_SAH) {
         // leaves in Morton order (the order the primitives are stored in): leaf i = sorted position i
@@ -1122,13 +1136,8 @@ int build_bvh(DeviceScene& ds, const rt_build_settings& bs, const DPrim* d_prims
     if (built) {
         // nodes are in place (GPU sweep: queued)
     } else if (choice == RT_BUILD_KARRAS) {
-        ds.build.builder = RT_BUILDER_KARRAS;
-        RT_CUDA(cudaMemsetAsync(visit, 0, sizeof(uint32_t) * n, stream));
-        if (n > 1) k_karras<<<gb, tb, 0, stream>>>(kin, (int)n, left, right, parent_internal, parent_leaf);
-        RT_CUDA(cudaEventRecord(ev[3], stream));
-        k_refit<<<gb, tb, 0, stream>>>((int)n, vin, box_lo, box_hi, left, right, parent_internal, parent_leaf, leaf_lo, leaf_hi, node_lo, node_hi, visit);
-        RT_CUDA(cudaEventRecord(ev[4], stream));
-        k_emit_nodes<<<gb, tb, 0, stream>>>((int)n, left, right, leaf_lo, leaf_hi, node_lo, node_hi, nodes);
+        const int rc = build_karras();
+        if (rc < 0) return rc;
     } else {
         // PLOC: cluster lists ping-pong between (cid_a, leaf_*) and (cid_b, node_*); `left`/`right` double as cid arrays,
         // `parent_internal` as the nearest-neighbour array.  The search radius trades differently per scene (flat rect
@@ -1209,9 +1218,13 @@ int build_bvh(DeviceScene& ds, const rt_build_settings& bs, const DPrim* d_prims
                 ds.build.builder = RT_BUILDER_PLOC;
             }
         }
-        if (!best_nodes) { set_error("bvh build: tree deeper than the traversal supports; commit with rt_build_settings::builder = RT_BUILD_KARRAS"); return RT_ERR_UNSUPPORTED; }
-        if (best_nodes == nodes_alt) { std::swap(ds.nodes, ds.nodes_alt); nodes = (BNode*)ds.nodes.p; }
-        RT_CUDA(cudaEventRecord(ev[4], stream));
+        if (!best_nodes) {   // every candidate deeper than the traversal supports
+            const int rc = build_karras();
+            if (rc < 0) return rc;
+        } else {
+            if (best_nodes == nodes_alt) { std::swap(ds.nodes, ds.nodes_alt); nodes = (BNode*)ds.nodes.p; }
+            RT_CUDA(cudaEventRecord(ev[4], stream));
+        }
     }
     k_permute_prims<<<gb, tb, 0, stream>>>(n, vin, d_prims_in, d_leaf_ids_in, prims_out, leaf_ids_out);
     RT_CUDA(cudaEventRecord(ev[5], stream));
