@@ -3,6 +3,7 @@
 #include "scene_host.h"
 #include "device_scene.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -60,6 +61,14 @@ int rt_tex_solid(rt_scene* s, float r, float g, float b) {
 
 int rt_tex_checker(rt_scene* s, int even_tex, int odd_tex) {
     CHECK_SCENE(s); CHECK_IX(even_tex, s->host.textures, "texture"); CHECK_IX(odd_tex, s->host.textures, "texture");
+    // the device resolves checker-of-checker chains iteratively, at most 8 levels (shade.cuh texture_value): refuse deeper
+    // nesting here instead of shading it black.  Textures only refer to earlier ones, so the depth is a simple recursion.
+    std::vector<int> depth(s->host.textures.size(), 0);
+    for (size_t i = 0; i < s->host.textures.size(); i++) {
+        const rt_flat_texture& x = s->host.textures[i];
+        if (x.type == RT_TEX_CHECKER) depth[i] = 1 + std::max(depth[x.a], depth[x.b]);
+    }
+    if (1 + std::max(depth[(size_t)even_tex], depth[(size_t)odd_tex]) > 8) return fail(RT_ERR_UNSUPPORTED, "checker textures nested more than 8 deep");
     rt_flat_texture t{}; t.type = RT_TEX_CHECKER; t.a = (uint32_t)even_tex; t.b = (uint32_t)odd_tex;
     return add_tex(s, t);
 }
@@ -77,6 +86,7 @@ int rt_perlin_tables(rt_scene* s, const float* ranvec768, const int32_t* perm768
 
 static int perlin_tex(rt_scene* s, uint32_t type, int perlin, float scale, int depth) {
     CHECK_SCENE(s); CHECK_IX(perlin, s->host.perlins, "perlin");
+    if (depth < 0 || depth > 64) return fail(RT_ERR_INVALID, "turbulence depth outside 0..64 (perlin::turb loops `depth` times per shaded hit)");
     rt_flat_texture t{}; t.type = type; t.a = (uint32_t)perlin; t.scale = scale; t.depth = depth;
     return add_tex(s, t);
 }

@@ -14,14 +14,14 @@ namespace {
 
 int fail(int code, const std::string& msg) { set_error(msg); return code; }
 
-uint32_t crc_table[256];
-bool crc_ready = false;
+// CRC-32 table, built once during static initialisation (thread-safe: rt_write_png may run on several threads)
+struct CrcTable {
+    uint32_t t[256];
+    CrcTable() { for (uint32_t i = 0; i < 256; i++) { uint32_t c = i; for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1; t[i] = c; } }
+};
+const CrcTable crc_table;
 uint32_t crc32_update(uint32_t crc, const uint8_t* p, size_t n) {
-    if (!crc_ready) {
-        for (uint32_t i = 0; i < 256; i++) { uint32_t c = i; for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1; crc_table[i] = c; }
-        crc_ready = true;
-    }
-    for (size_t i = 0; i < n; i++) crc = crc_table[(crc ^ p[i]) & 0xff] ^ (crc >> 8);
+    for (size_t i = 0; i < n; i++) crc = crc_table.t[(crc ^ p[i]) & 0xff] ^ (crc >> 8);
     return crc;
 }
 void put_be32(std::vector<uint8_t>& v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }

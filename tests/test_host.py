@@ -130,6 +130,24 @@ def test_error_behaviour_is_codes_not_exit():
     g = helpers.load_golden("basic")
     with pytest.raises(rt.RtError, match="truncated"):
         rt.Scene().replay(g["program"][:20])
+    # parameters that drive device loops are validated where the scene is recorded
+    t = rt.Scene()
+    pn = t.perlin_tables(np.ones(768, np.float32), np.zeros(768, np.int32))
+    with pytest.raises(rt.RtError, match="turbulence depth"):
+        t.tex_turbulent(pn, 1.0, 0x7fffffff)
+    with pytest.raises(rt.RtError, match="turbulence depth"):
+        t.tex_turbulent(pn, 1.0, -1)
+    assert t.tex_turbulent(pn, 1.0, 7) >= 0
+    c = t.tex_solid(0, 0, 0)
+    for _ in range(8):
+        c = t.tex_checker(c, c)
+    with pytest.raises(rt.RtError, match="nested more than 8"):
+        t.tex_checker(c, c)
+    # an idempotent flatten keeps the flattening (and with it a committed device copy) current; an edit invalidates it
+    h1 = s.scene_hash()
+    assert s.flatten() == 1 and s.scene_hash() == h1
+    s.set_background(0.1, 0.2, 0.3)
+    assert s.flatten() == 1 and s.scene_hash() != h1
 
 
 def test_nested_medium_is_rejected():
