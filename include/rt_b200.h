@@ -172,6 +172,17 @@ int rt_scene_bvh_nodes(rt_scene* s, void* buf, size_t cap_bytes);
  * prim_id: DFS leaf id or -1; t: hit distance (+inf on miss). */
 int rt_first_hit(rt_scene* s, const float* rays, int n, float t_min, const float* xi, int32_t* prim_id, float* t);
 
+/* rt_first_hit without any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and results as rt_first_hit, bit for bit; the device staging of the rays and of the results lives in a
+ * file-scope __device__ array of RT_FIRST_HIT_STATIC_MAX rays (2.5 MiB, held by every GPU that loads the library until the
+ * process exits) instead of a buffer the scene grows.  n > RT_FIRST_HIT_STATIC_MAX is rejected with RT_ERR_INVALID.  The
+ * call makes no cudaMalloc / cudaFree (the scene must already be committed — rt_scene_commit allocates).  Every call, from
+ * every scene on the same GPU, shares the one array, which keeps the last call's contents: calls that overlap on a GPU
+ * race — serialise them (the call itself returns only after its results are in host memory). */
+#define RT_FIRST_HIT_STATIC_MAX 65536
+int rt_first_hit_static(rt_scene* s, const float* rays, int n, float t_min, const float* xi, int32_t* prim_id, float* t);
+
 enum rt_render_flags {
     RT_RENDER_DEFAULT = 0,
     RT_RENDER_COUNTERS = 1, /* fill the traversal counters in rt_render_stats (slower) */

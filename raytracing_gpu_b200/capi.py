@@ -119,7 +119,7 @@ def lib():
         "rt_image_height": (i32, [i32, f32]), "rt_scene_commit": (i32, [vp, i32, C.POINTER(BuildStats)]),
         "rt_scene_commit_ex": (i32, [vp, i32, C.POINTER(BuildSettings), C.POINTER(BuildStats)]),
         "rt_measure_fp32_peak": (i32, [i32, C.POINTER(C.c_double)]), "rt_scene_bvh_nodes": (i32, [vp, vp, C.c_size_t]),
-        "rt_first_hit": (i32, [vp, vp, i32, f32, vp, vp, vp]),
+        "rt_first_hit": (i32, [vp, vp, i32, f32, vp, vp, vp]), "rt_first_hit_static": (i32, [vp, vp, i32, f32, vp, vp, vp]),
         "rt_render": (i32, [vp, C.POINTER(RenderSettings), vp, C.POINTER(RenderStats)]),
         "rt_render_device": (i32, [vp, C.POINTER(RenderSettings), vp, vp, C.POINTER(RenderStats)]),
         "rt_quantize_frame": (i32, [vp, i32, i32, vp]),
@@ -339,13 +339,14 @@ class Scene:
                 _check(rc)
             cap *= 8
 
-    def first_hit(self, rays, t_min=0.001, xi=None):
+    def first_hit(self, rays, t_min=0.001, xi=None, static=False):
+        """rt_first_hit; static=True: rt_first_hit_static (no allocation, at most RT_FIRST_HIT_STATIC_MAX rays)."""
         rays = _f32(rays).reshape(-1, 7)
         n = rays.shape[0]
         ids = np.empty(n, np.int32)
         t = np.empty(n, np.float32)
         xi_a = _f32(xi) if xi is not None else None
-        _check(lib().rt_first_hit(self._h, rays.ctypes.data, n, float(t_min), xi_a.ctypes.data if xi_a is not None else None,
+        _check((lib().rt_first_hit_static if static else lib().rt_first_hit)(self._h, rays.ctypes.data, n, float(t_min), xi_a.ctypes.data if xi_a is not None else None,
                                   ids.ctypes.data, t.ctypes.data))
         return ids, t
 

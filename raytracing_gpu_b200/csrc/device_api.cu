@@ -255,6 +255,43 @@ __global__ void k_first_hit(SceneView sv, const float* rays, int n, float t_min,
     out_t[i] = c.t;
 }
 
+// ---- rt_first_hit_static: the first-hit query with its device staging in a file-scope array (no allocation per call) ----
+// Layout of the array: rays [7 n] | xi [n] | t [n] | id [n], each section at a 256-byte boundary for n = RT_FIRST_HIT_STATIC_MAX.
+constexpr size_t FHS_MAX = RT_FIRST_HIT_STATIC_MAX;
+constexpr size_t FHS_OFF_XI = sizeof(float) * 7 * FHS_MAX, FHS_OFF_T = FHS_OFF_XI + sizeof(float) * FHS_MAX,
+                 FHS_OFF_ID = FHS_OFF_T + sizeof(float) * FHS_MAX, FHS_BYTES = FHS_OFF_ID + sizeof(int32_t) * FHS_MAX;
+static_assert(FHS_OFF_XI % 256 == 0 && FHS_OFF_T % 256 == 0 && FHS_OFF_ID % 256 == 0, "sections stay 256-byte aligned");
+static __device__ __align__(256) unsigned char g_first_hit_scratch[FHS_BYTES];   // 2.5 MiB on every GPU that loads the library, until exit
+
+// the same query as k_first_hit; device code names the array directly
+__global__ void k_first_hit_static(SceneView sv, int n, float t_min, int with_xi) {
+    const float* rays = reinterpret_cast<const float*>(g_first_hit_scratch);
+    const float* xi = with_xi ? reinterpret_cast<const float*>(g_first_hit_scratch + FHS_OFF_XI) : nullptr;
+    float* out_t = reinterpret_cast<float*>(g_first_hit_scratch + FHS_OFF_T);
+    int32_t* out_id = reinterpret_cast<int32_t*>(g_first_hit_scratch + FHS_OFF_ID);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = i < n;
+    Ray r; r.o = make_float3(0.f, 0.f, 0.f); r.d = make_float3(0.f, 0.f, 1.f); r.tm = 0.f;
+    float x = 1.0f;
+    if (active) {
+        const float* q = rays + 7 * (size_t)i;
+        r.o = make_float3(q[0], q[1], q[2]); r.d = make_float3(q[3], q[4], q[5]); r.tm = q[6];
+        if (xi) x = xi[i];
+    }
+    const Closest c = closest_hit<false, TV_PLAIN, 1>(sv, r, t_min, xi != nullptr, [x](uint32_t) { return x; }, nullptr, active, nullptr);
+    if (!active) return;
+    int32_t id = -1;
+    if (c.prim >= 0) id = (int32_t)sv.prim_leaf_id[c.prim];
+    else if (c.prim <= -2) id = (int32_t)sv.media[-2 - c.prim].leaf_id;
+    out_id[i] = id;
+    out_t[i] = c.t;
+}
+
+// HOST address of the array on each device: in host code the array's name is a stand-in, not a device address — it is
+// looked up once per device, with that device current (cudaGetSymbolAddress), and cached
+constexpr int FHS_MAX_DEVICES = 64;
+unsigned char* g_fhs_addr[FHS_MAX_DEVICES] = {};
+
 } // namespace
 
 // The device copy must describe the scene as it is NOW: an edit (or rt_set_semantics) after the commit would otherwise
@@ -308,6 +345,37 @@ extern "C" int rt_scene_bvh_nodes(rt_scene* s, void* buf, size_t cap) {
     RT_CUDA(cudaSetDevice(ds->device));
     if (bytes) RT_CUDA(cudaMemcpy(buf, ds->view.nodes, bytes, cudaMemcpyDeviceToHost));
     return (int)ds->view.n_nodes;
+}
+
+extern "C" int rt_first_hit_static(rt_scene* s, const float* rays, int n, float t_min, const float* xi, int32_t* prim_id, float* t) {
+    if (!s || !rays || !prim_id || !t || n < 0) { set_error("first_hit_static: bad argument"); return RT_ERR_INVALID; }
+    if ((size_t)n > FHS_MAX) {
+        set_error("first_hit_static: n exceeds RT_FIRST_HIT_STATIC_MAX (65536 rays per call): split the ray set or use rt_first_hit");
+        return RT_ERR_INVALID;
+    }
+    DeviceScene* ds = nullptr;
+    const int rc = device_scene_current(s, &ds, "first_hit_static");
+    if (rc < 0) return rc;
+    if (n == 0) return RT_OK;
+    if (ds->device < 0 || ds->device >= FHS_MAX_DEVICES) { set_error("first_hit_static: device index out of range"); return RT_ERR_INVALID; }
+    RT_CUDA(cudaSetDevice(ds->device));
+    unsigned char*& base = g_fhs_addr[ds->device];
+    if (!base) {   // once per device, with that device current
+        void* p = nullptr;
+        RT_CUDA(cudaGetSymbolAddress(&p, g_first_hit_scratch));
+        base = (unsigned char*)p;
+    }
+    const size_t nn = (size_t)n;
+    cudaStream_t st = ds->stream;
+    RT_CUDA(cudaMemcpyAsync(base, rays, sizeof(float) * 7 * nn, cudaMemcpyHostToDevice, st));
+    if (xi) RT_CUDA(cudaMemcpyAsync(base + FHS_OFF_XI, xi, sizeof(float) * nn, cudaMemcpyHostToDevice, st));
+    // nothing in the array has to start at zero: every word the kernel reads was just written, every output word below n is overwritten
+    k_first_hit_static<<<(n + 127) / 128, 128, 0, st>>>(ds->view, n, t_min, xi ? 1 : 0);
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(prim_id, base + FHS_OFF_ID, sizeof(int32_t) * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(t, base + FHS_OFF_T, sizeof(float) * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
 }
 
 extern "C" int rt_first_hit(rt_scene* s, const float* rays, int n, float t_min, const float* xi, int32_t* prim_id, float* t) {
