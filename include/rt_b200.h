@@ -224,7 +224,7 @@ enum rt_traversal_bits { RT_TRAVERSAL_FORCE = 0x100, RT_TRAVERSAL_DEFAULT_BITS =
 enum rt_debug_flags {
     RT_DEBUG_NO_GRAPH = 1,     /* direct kernel launches instead of the CUDA graph of 8 iterations */
     RT_DEBUG_RASTER_FILM = 2,  /* samples walk the film row by row instead of in 8x4 tiles */
-    RT_DEBUG_BLOCK_SHADE = 4   /* round 1's block-tile shade kernel (same-box A/B of the warp-tile kernel) */
+    RT_DEBUG_WARP_SHADE = 4    /* the barrier-free warp-tile shade kernel (measured slower than the block-tile default: A/B only) */
 };
 
 typedef struct rt_render_stats {

@@ -403,9 +403,22 @@ __device__ __forceinline__ bool shade_path(const SceneView& sv, const PoolView& 
     return true;
 }
 
+#ifndef RT_WTILE
+#define RT_WTILE 128
+#endif
+#ifndef RT_SHADE_MIN_BLOCKS
+#define RT_SHADE_MIN_BLOCKS 4
+#endif
 constexpr int SHADE_BLOCK = 256, SHADE_WARPS = SHADE_BLOCK / 32;
-constexpr int WTILE = 256, WROUNDS = WTILE / 32;       // paths per warp tile / rounds of 32
+constexpr int WTILE = RT_WTILE, WROUNDS = WTILE / 32;       // paths per warp tile / rounds of 32
 
+// Warp-tile shade (RT_DEBUG_WARP_SHADE): round 2's attempt to remove the block-wide barriers of the block-tile kernel below
+// (37 % of its stall samples).  A warp ranks a tile of RT_WTILE paths by class with ballots, allocates for the tile BEFORE it
+// shades (possible because the class byte says whether a path can continue) and shades RT_WTILE / 32 rounds — no
+// __syncthreads at all.  Measured same-box against the block-tile kernel (profiles/r02_shade_ab.md), best of seven
+// tile-size / occupancy points: final scene 29.5 vs 27.1 ms per 128 spp, Cornell smoke 23.9 vs 23.3, big_scene1 1.00 vs 0.78,
+// 1 M-triangle mesh 12.7 vs 12.3 — the barriers were not what the kernel waits for; a warp that owns its whole tile
+// serialises RT_WTILE / 32 dependent-load chains that eight warps of a block overlap.  Kept as an A/B switch, not the default.
 template <bool DEFER>
 __device__ __forceinline__ void shade_warp_tiles(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
     __shared__ uint32_t s_perm[SHADE_WARPS][WTILE];   // sorted rank -> tile-local index | class byte << 8 | rank among the continuing (or ending) paths << 12
@@ -505,12 +518,12 @@ __device__ __forceinline__ void shade_warp_tiles(const SceneView& sv, const Pool
     }
 }
 
-__global__ void __launch_bounds__(SHADE_BLOCK) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<false>(sv, pv, fp, cur); }
+__global__ void __launch_bounds__(SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<false>(sv, pv, fp, cur); }
 // shade of the deferred extend: holes in the tiles and the finished-resumed region behind the pool
-__global__ void __launch_bounds__(SHADE_BLOCK) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<true>(sv, pv, fp, cur); }
+__global__ void __launch_bounds__(SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<true>(sv, pv, fp, cur); }
 
-// Round 1's shade, kept for the same-box A/B (RT_DEBUG_BLOCK_SHADE): a BLOCK sorts a 256-path tile by class in shared
-// memory, thread 0 allocates between two barriers — five __syncthreads per tile.
+// The default shade: a BLOCK sorts a 256-path tile by class in shared memory (a warp shades one class), thread 0 allocates
+// between two barriers — five __syncthreads per tile.
 template <bool DEFER>
 __device__ __forceinline__ void shade_block_tiles(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
     constexpr int NC = 8;
@@ -777,7 +790,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     }
     const bool count = (st.flags & RT_RENDER_COUNTERS) != 0;
     const bool timers = (st.flags & RT_RENDER_TIMERS) != 0;
-    const bool block_shade = (st.debug_flags & RT_DEBUG_BLOCK_SHADE) != 0;
+    const bool block_shade = (st.debug_flags & RT_DEBUG_WARP_SHADE) == 0;   // the default: see the note above shade_warp_tiles
 
     const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
     const FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, st.debug_flags, total, npix, magic, d_accum, st.tile_index, tile_count};

@@ -49,12 +49,15 @@ def run(label, **kw):
 print(json.dumps({"workload": desc, "prims": st.n_prims, "builder": st.builder, "bvh_depth": st.bvh_depth, "sah": st.sah_internal,
                   "build_ms": st.ms_total, "host_ms": st.ms_host}), flush=True)
 deferred = st.n_prims >= 65536
-run("default")
-run("block_shade", debug_flags=rt.capi.DEBUG_BLOCK_SHADE)
+tag = os.path.basename(rt.lib_path())
+run(f"default [{tag}]")
+run("warp_shade", debug_flags=rt.capi.DEBUG_WARP_SHADE)
+if os.environ.get("AB_ONLY_DEFAULT"):
+    sys.exit(0)
 if not deferred:
     for v in range(8):
         run(f"traversal_{v}" + "".join(s for b, s in ((1, "+tcull"), (2, "+smem"), (4, "+minmax")) if v & b), traversal=F | v)
-    run("traversal_4+block_shade (= round 1)", traversal=F | 4, debug_flags=rt.capi.DEBUG_BLOCK_SHADE)
+    run("traversal_4 (= round 1 kernels)", traversal=F | 4)
 else:
     run("defer_off", extend_defer=rt.capi.DEFER_OFF)
-    run("defer_off+block_shade", extend_defer=rt.capi.DEFER_OFF, debug_flags=rt.capi.DEBUG_BLOCK_SHADE)
+    run("defer_off+warp_shade", extend_defer=rt.capi.DEFER_OFF, debug_flags=rt.capi.DEBUG_WARP_SHADE)
