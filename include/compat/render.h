@@ -27,6 +27,7 @@ struct render_settings {
 namespace rtc {
 inline const char*& draw_output_path() { static const char* p = "image.png"; return p; }   // render.h:168 writes "image.png"
 inline int& draw_device() { static int d = 0; return d; }
+inline unsigned& draw_devices() { static unsigned n = RT_DRAW_ALL_DEVICES; return n; }   // draw() renders on every visible GPU by default
 }
 
 // Scene = the reference's `scene` (scenes.h:36-79) or anything with d_world / d_camera / background
@@ -42,6 +43,7 @@ void draw(Scene& curr_scene, render_settings settings) {
     st.max_depth = settings.max_depth;
     st.seed = 1984;                                     // render.h:91
     st.device = (uint32_t)rtc::draw_device();
+    st.n_devices = rtc::draw_devices();
     std::cerr << "\rRendering " << settings.no_fb << " frame buffers        " << std::flush;
     if (rt_draw(rtc::sc(), &st, rtc::draw_output_path(), nullptr, nullptr, nullptr) < 0) {
         std::cerr << "rt_b200 error: " << rt_last_error() << std::endl;        // the reference would exit(99) (common.h:30-38)

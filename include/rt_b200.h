@@ -252,6 +252,38 @@ int rt_render(rt_scene* s, const rt_render_settings* settings, float* out_rgb, r
 int rt_render_device(rt_scene* s, const rt_render_settings* settings, float* d_accum_rgb, void* cuda_stream,
                      rt_render_stats* stats_or_null);
 
+/* ---- multi-GPU behind the boundary: replaces draw()'s single `render<<<>>>` (render.h:118-162) ----
+ * One host thread per device: the scene is committed on every device it is not current on (replicated: a deterministic
+ * build is cheaper than a broadcast), every device renders its share into a zero-initialised W*H*3 float buffer — a
+ * contiguous sample range (RT_SPLIT_SAMPLE) or the film blocks b with b % n == k (RT_SPLIT_TILE) — and the root device
+ * (device_ids[0]) finishes with ONE reduce: a hand-written kernel that reads the other devices' buffers through NVLink
+ * peer mappings and sums them in device order (bitwise reproducible for a given device count), scales by 1/samples and
+ * writes the frame.  Without peer access the buffers are staged through cudaMemcpyPeer.  Philox keys make the sample set
+ * independent of the split; float summation order differs with the device count (~1e-6 relative). */
+enum rt_split_mode { RT_SPLIT_SAMPLE = 0, RT_SPLIT_TILE = 1 };
+#define RT_MAX_DEVICES 16
+typedef struct rt_multi_settings {
+    uint32_t n_devices;                    /* 0 = every visible CUDA device, in order */
+    int32_t device_ids[RT_MAX_DEVICES];    /* used when n_devices > 0; [0] is the root */
+    uint32_t split_mode;                   /* rt_split_mode */
+    uint32_t reserved[6];
+} rt_multi_settings;
+typedef struct rt_multi_stats {
+    uint32_t n_devices;
+    uint32_t peer_reduce;                  /* 1: the reduce kernel read peer memory directly; 0: staged copies */
+    float ms_commit_max;                   /* slowest device's commit (0 where the device copy was current) */
+    float ms_render[RT_MAX_DEVICES];       /* per device: first ray-gen launch -> its accumulation complete (CUDA events) */
+    float ms_reduce;                       /* the reduce + scale kernel on the root (CUDA events) */
+    float ms_wall;                         /* host wall clock of the call: commit + render + reduce + D2H */
+    uint64_t samples, rays;                /* summed over the devices */
+    uint64_t reserved[4];
+} rt_multi_stats;
+/* out_rgb: width*height*3 floats, host memory, linear means over the sample range [sample_first, sample_first + sample_count)
+ * of `settings` (like rt_render: sample_count 0 = up to samples_per_pixel); that range is what is split over the devices.
+ * settings->tile_index / tile_count must be 0.  multi_or_null == NULL: every visible device, sample-split. */
+int rt_render_multi(rt_scene* s, const rt_render_settings* settings, const rt_multi_settings* multi_or_null, float* out_rgb,
+                    rt_multi_stats* stats_or_null);
+
 /* FP32 peak of `device` measured with an FMA microbenchmark (the denominator of bench.py's roofline_fp32). */
 int rt_measure_fp32_peak(int device, double* tflops);
 

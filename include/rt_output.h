@@ -56,9 +56,12 @@ typedef struct rt_draw_settings {      /* render_settings, render.h:21-30 */
     uint32_t no_fb;                    /* default 10 */
     uint32_t max_depth;                /* default 50 */
     uint32_t seed;                     /* Philox key (the reference hard-codes 1984, render.h:91) */
-    uint32_t device;                   /* CUDA device used when the scene is not committed yet */
-    uint32_t reserved[8];
+    uint32_t device;                   /* CUDA device used when the scene is not committed yet (n_devices <= 1) */
+    uint32_t n_devices;                /* 0 / 1: one GPU (`device`); RT_DRAW_ALL_DEVICES: every visible GPU; n: devices 0 .. n-1.
+                                          Each batch is then sample-split over the GPUs and reduced on the first (rt_render_multi) */
+    uint32_t reserved[7];
 } rt_draw_settings;
+#define RT_DRAW_ALL_DEVICES 0xffffffffu
 
 /* draw(scene, settings) (render.h:118-174) minus the temp directory: renders no_fb batches of
  * samples_per_pixel_per_fb samples each (batch i = sample indices [i*spp, (i+1)*spp)), quantises every batch mean,

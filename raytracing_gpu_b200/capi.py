@@ -55,6 +55,18 @@ TRAVERSAL_FORCE = 0x100
 DEBUG_NO_GRAPH, DEBUG_RASTER_FILM, DEBUG_WARP_SHADE = 1, 2, 4
 
 
+class MultiSettings(C.Structure):
+    _fields_ = [("n_devices", C.c_uint32), ("device_ids", C.c_int32 * 16), ("split_mode", C.c_uint32), ("reserved", C.c_uint32 * 6)]
+
+
+class MultiStats(C.Structure):
+    _fields_ = [("n_devices", C.c_uint32), ("peer_reduce", C.c_uint32), ("ms_commit_max", C.c_float), ("ms_render", C.c_float * 16),
+                ("ms_reduce", C.c_float), ("ms_wall", C.c_float), ("samples", C.c_uint64), ("rays", C.c_uint64), ("reserved", C.c_uint64 * 4)]
+
+
+SPLIT_SAMPLE, SPLIT_TILE = 0, 1
+
+
 class CatalogParams(C.Structure):
     _fields_ = [("image", C.c_void_p), ("image_width", C.c_int), ("image_height", C.c_int), ("image_bytes_per_pixel", C.c_int),
                 ("aspect", C.c_float), ("vertices", C.c_void_p), ("n_vertices", C.c_int), ("indices", C.c_void_p),
@@ -64,7 +76,7 @@ class CatalogParams(C.Structure):
 class DrawSettings(C.Structure):
     _fields_ = [("image_width", C.c_uint32), ("image_height", C.c_uint32), ("aspect_ratio", C.c_float),
                 ("samples_per_pixel_per_fb", C.c_uint32), ("no_fb", C.c_uint32), ("max_depth", C.c_uint32),
-                ("seed", C.c_uint32), ("device", C.c_uint32), ("reserved", C.c_uint32 * 8)]
+                ("seed", C.c_uint32), ("device", C.c_uint32), ("n_devices", C.c_uint32), ("reserved", C.c_uint32 * 7)]
 
 
 class CheckpointInfo(C.Structure):
@@ -123,6 +135,7 @@ def lib():
         "rt_render": (i32, [vp, C.POINTER(RenderSettings), vp, C.POINTER(RenderStats)]),
         "rt_render_device": (i32, [vp, C.POINTER(RenderSettings), vp, vp, C.POINTER(RenderStats)]),
         "rt_quantize_frame": (i32, [vp, i32, i32, vp]),
+        "rt_render_multi": (i32, [vp, C.POINTER(RenderSettings), C.POINTER(MultiSettings), vp, C.POINTER(MultiStats)]),
         "rt_catalog_scene": (i32, [vp, C.c_char_p, C.POINTER(CatalogParams), C.POINTER(C.c_float)]),
         # include/rt_obj.h
         "rt_obj_load": (i32, [C.c_char_p, C.POINTER(vp)]), "rt_obj_parse": (i32, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.POINTER(vp)]),
@@ -361,6 +374,20 @@ class Scene:
         _check(lib().rt_render(self._h, C.byref(st), out.ctypes.data, C.byref(stats)))
         return out, stats
 
+    def render_multi(self, width, height, spp, devices=None, split="sample", max_depth=50, seed=1984, pool_paths=0):
+        """rt_render_multi: one frame on several GPUs of this node (devices=None: every visible one; devices[0] is the root
+        that reduces).  Returns (image, MultiStats)."""
+        st = RenderSettings(width=width, height=height, samples_per_pixel=spp, max_depth=max_depth, seed=seed, pool_paths=pool_paths)
+        ms = MultiSettings(split_mode={"sample": SPLIT_SAMPLE, "tile": SPLIT_TILE}[split])
+        if devices is not None:
+            ms.n_devices = len(devices)
+            for k, d in enumerate(devices):
+                ms.device_ids[k] = int(d)
+        out = np.empty((height, width, 3), np.float32)
+        stats = MultiStats()
+        _check(lib().rt_render_multi(self._h, C.byref(st), C.byref(ms), out.ctypes.data, C.byref(stats)))
+        return out, stats
+
     def scene_hash(self):
         h = C.c_uint64()
         _check(lib().rt_scene_hash(self._h, C.byref(h)))
@@ -377,10 +404,11 @@ class Scene:
         return stats
 
     def draw(self, image_width, aspect_ratio, samples_per_pixel_per_fb, no_fb, max_depth=50, seed=1984, png_path=None,
-             image_height=0, device=0):
+             image_height=0, device=0, n_devices=0):
         """include/rt_output.h rt_draw: the reference's draw() (render.h:118) — batches, 8-bit quantisation, averaging, PNG."""
         st = DrawSettings(image_width=image_width, image_height=image_height, aspect_ratio=aspect_ratio,
-                          samples_per_pixel_per_fb=samples_per_pixel_per_fb, no_fb=no_fb, max_depth=max_depth, seed=seed, device=device)
+                          samples_per_pixel_per_fb=samples_per_pixel_per_fb, no_fb=no_fb, max_depth=max_depth, seed=seed, device=device,
+                          n_devices=n_devices)
         h = image_height or (image_height_of(image_width, aspect_ratio) if aspect_ratio > 0 and image_width > 0 else 0)
         out = np.empty((max(h, 1), max(image_width, 1), 3), np.uint8)
         hh = C.c_uint32()

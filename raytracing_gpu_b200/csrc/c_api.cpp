@@ -15,13 +15,16 @@ using namespace rtb;
 struct rt_scene {
     HostScene host;
     DeviceScene* dev = nullptr;   // created by rt_scene_commit
+    std::vector<DeviceScene*> replicas;   // further device copies made by rt_render_multi (one per extra device)
 };
 
 namespace rtb {
 static thread_local std::string g_err;
 void set_error(const std::string& e) { g_err = e; }
+std::string last_error_copy() { return g_err; }
 HostScene& host_of(rt_scene* s) { return s->host; }
 DeviceScene*& device_of(rt_scene* s) { return s->dev; }
+std::vector<DeviceScene*>& replicas_of(rt_scene* s) { return s->replicas; }
 } // namespace rtb
 
 static int fail(int code, const char* msg) { g_err = msg; return code; }
@@ -43,6 +46,7 @@ int rt_scene_create(rt_scene** out) {
 void rt_scene_destroy(rt_scene* s) {
     if (!s) return;
     if (s->dev) device_scene_destroy(s->dev);
+    for (DeviceScene* r : s->replicas) device_scene_destroy(r);
     delete s;
 }
 

@@ -296,11 +296,16 @@ unsigned char* g_fhs_addr[FHS_MAX_DEVICES] = {};
 
 // The device copy must describe the scene as it is NOW: an edit (or rt_set_semantics) after the commit would otherwise
 // render — and checkpoint under the new rt_scene_hash — the old scene without a word.
+bool device_scene_describes(rt_scene* s, const DeviceScene& ds) {
+    const HostScene& hs = host_of(s);
+    return ds.committed_generation && hs.flat.valid && hs.flat.generation == ds.committed_generation && hs.semantics == ds.committed_semantics;
+}
 bool device_scene_is_current(rt_scene* s) {
     const DeviceScene* ds = device_of(s);
-    const HostScene& hs = host_of(s);
-    return ds && ds->committed_generation && hs.flat.valid && hs.flat.generation == ds->committed_generation && hs.semantics == ds->committed_semantics;
+    return ds && device_scene_describes(s, *ds);
 }
+DeviceScene* device_scene_new() { return new DeviceScene; }
+int commit_device_scene(rt_scene* s, DeviceScene& ds, int device, const rt_build_settings& bs) { return commit_impl(host_of(s), ds, device, bs); }
 
 int device_scene_current(rt_scene* s, DeviceScene** out, const char* who) {
     DeviceScene* ds = device_of(s);

@@ -155,6 +155,13 @@ int compute_medium_bounds(DeviceScene& ds, DMedium* media, float time_lo, float 
 // wavefront.cu
 void render_pool_destroy(struct RenderPool* p);
 
+// device_api.cu / wavefront.cu: pieces rt_render_multi (multi_gpu.cu) drives per device
+int commit_device_scene(rt_scene* s, DeviceScene& ds, int device, const rt_build_settings& bs);
+int render_device_scene(DeviceScene& ds, const rt_render_settings& st, float* d_accum, cudaStream_t stream, rt_render_stats* stats);
+DeviceScene* device_scene_new();
+bool device_scene_describes(rt_scene* s, const DeviceScene& ds);   // committed from the scene's current flattening and semantics
+std::string last_error_copy();
+
 // device_api.cu: the scene's device copy, provided it describes the scene as it is now (RT_ERR_STATE otherwise)
 int device_scene_current(rt_scene* s, DeviceScene** out, const char* who);
 

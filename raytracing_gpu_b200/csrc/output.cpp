@@ -186,7 +186,14 @@ int rt_draw(rt_scene* scene, const rt_draw_settings* st, const char* png_path, u
         if (h <= 0) return fail(RT_ERR_INVALID, "draw: computed image height is not positive");
         height = (uint32_t)h;
     }
-    if (!device_scene_is_current(scene)) { const int rc = rt_scene_commit(scene, (int)st->device, nullptr); if (rc < 0) return rc; }   // draw() takes the scene as it is now
+    const bool multi = st->n_devices > 1;
+    rt_multi_settings mset{};
+    if (multi && st->n_devices != RT_DRAW_ALL_DEVICES) {
+        if (st->n_devices > RT_MAX_DEVICES) return fail(RT_ERR_INVALID, "draw: n_devices exceeds RT_MAX_DEVICES");
+        mset.n_devices = st->n_devices;
+        for (uint32_t k = 0; k < st->n_devices; k++) mset.device_ids[k] = (int32_t)k;
+    }
+    if (!multi && !device_scene_is_current(scene)) { const int rc = rt_scene_commit(scene, (int)st->device, nullptr); if (rc < 0) return rc; }   // draw() takes the scene as it is now
     const size_t n = (size_t)width * height * 3;
     std::vector<float> fb(n);
     std::vector<uint8_t> frames(n * no_fb), final_px(n);
@@ -195,7 +202,13 @@ int rt_draw(rt_scene* scene, const rt_draw_settings* st, const char* png_path, u
         rt_render_settings rs{};
         rs.width = width; rs.height = height; rs.samples_per_pixel = spp * no_fb; rs.max_depth = st->max_depth ? st->max_depth : 50u;
         rs.seed = st->seed; rs.sample_first = i * spp; rs.sample_count = spp;
-        const int rc = rt_render(scene, &rs, fb.data(), &one);                 // mean of this batch (render.h:112)
+        int rc;
+        if (multi) {   // the batch's sample range is split over the GPUs and reduced on the first
+            rt_multi_stats mst{};
+            rc = rt_render_multi(scene, &rs, &mset, fb.data(), &mst);
+            one = rt_render_stats{};
+            one.samples = mst.samples; one.rays = mst.rays; one.ms_total = mst.ms_wall;
+        } else rc = rt_render(scene, &rs, fb.data(), &one);                    // mean of this batch (render.h:112)
         if (rc < 0) return rc;
         total.samples += one.samples; total.rays += one.rays; total.iterations += one.iterations; total.kernel_launches += one.kernel_launches;
         total.ms_total += one.ms_total;

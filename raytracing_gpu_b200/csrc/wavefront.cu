@@ -914,6 +914,12 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
 } // namespace
 } // namespace rtb
 
+namespace rtb {
+int render_device_scene(DeviceScene& ds, const rt_render_settings& st, float* d_accum, cudaStream_t stream, rt_render_stats* stats) {
+    return render_impl(ds, st, d_accum, stream, stats);
+}
+} // namespace rtb
+
 using namespace rtb;
 
 extern "C" int rt_render_device(rt_scene* s, const rt_render_settings* st, float* d_accum, void* cuda_stream, rt_render_stats* stats) {

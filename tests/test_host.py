@@ -130,6 +130,8 @@ def test_error_behaviour_is_codes_not_exit():
     g = helpers.load_golden("basic")
     with pytest.raises(rt.RtError, match="truncated"):
         rt.Scene().replay(g["program"][:20])
+    with pytest.raises(rt.RtError):                      # no device in this container / bad split refused before any work
+        s.render_multi(8, 8, 1, split="tile", devices=[0])
     # parameters that drive device loops are validated where the scene is recorded
     t = rt.Scene()
     pn = t.perlin_tables(np.ones(768, np.float32), np.zeros(768, np.int32))
