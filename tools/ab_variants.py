@@ -58,6 +58,8 @@ if not deferred:
     for v in range(8):
         run(f"traversal_{v}" + "".join(s for b, s in ((1, "+tcull"), (2, "+smem"), (4, "+minmax")) if v & b), traversal=F | v)
     run("traversal_4 (= round 1 kernels)", traversal=F | 4)
+    for below in (4, 8, 12):
+        run(f"defer_{below}", extend_defer=below + 1)
 else:
     run("defer_off", extend_defer=rt.capi.DEFER_OFF)
     run("defer_off+warp_shade", extend_defer=rt.capi.DEFER_OFF, debug_flags=rt.capi.DEBUG_WARP_SHADE)
