@@ -131,7 +131,8 @@ typedef struct rt_build_stats {
     uint32_t builder;        /* rt_builder: which hierarchy builder produced the tree */
     uint32_t n_wide_nodes;   /* > 0: the traversal walks the compressed 4-wide layout (this many 64-byte nodes) */
     float ms_host;           /* host wall clock of the whole rt_scene_commit call */
-    uint32_t reserved[1];
+    float ms_wide;           /* collapse of the binary tree into wide nodes (CUDA events; not part of ms_total) */
+    uint32_t wide_depth;     /* levels of the wide tree */
 } rt_build_stats;
 
 /* How rt_scene_commit_ex builds the acceleration structure.  Zero-initialise for the defaults.  (Round 1 read these
@@ -150,7 +151,8 @@ typedef struct rt_build_settings {
     uint32_t sah_max_prims;  /* RT_BUILD_AUTO: largest scene the SAH sweep takes; 0 = 65536 */
     uint32_t ploc_radius;    /* PLOC neighbour search radius; 0 = chosen per scene */
     uint32_t ploc_top;       /* PLOC hands the top of the tree to the SAH sweep once this many clusters are left; 0 = 32768 */
-    uint32_t wide_nodes;     /* rt_wide_choice: collapse the binary tree into 4-wide nodes with 8-bit child boxes */
+    uint32_t wide_nodes;     /* rt_wide_choice: collapse the binary tree into 4-wide nodes with 8-bit child boxes.
+                                AUTO = scenes of 65 536 primitives and more (the binary tree no longer fits the L1) */
     uint32_t flags;          /* rt_build_flags */
     uint32_t reserved[10];
 } rt_build_settings;

@@ -37,7 +37,7 @@ class BuildStats(C.Structure):
                 ("ms_sort", C.c_float), ("ms_hierarchy", C.c_float), ("ms_refit", C.c_float),
                 ("ms_collapse", C.c_float), ("ms_total", C.c_float), ("bvh_depth", C.c_uint32), ("build_rounds", C.c_uint32),
                 ("sah_internal", C.c_float), ("ploc_radius", C.c_uint32), ("builder", C.c_uint32),
-                ("n_wide_nodes", C.c_uint32), ("ms_host", C.c_float), ("reserved", C.c_uint32 * 1)]
+                ("n_wide_nodes", C.c_uint32), ("ms_host", C.c_float), ("ms_wide", C.c_float), ("wide_depth", C.c_uint32)]
 
 
 class BuildSettings(C.Structure):

@@ -841,6 +841,101 @@ __global__ void __launch_bounds__(SAH_THREADS) k_sah_level(SahArgs A, uint32_t l
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Collapse of the binary tree into 4-wide nodes with 8-bit child boxes (WNode, device_scene.cuh)
+//
+// Top-down, level by level, one thread per wide node: the node starts with the two children of its binary node and
+// replaces, while it has fewer than four, its internal child of largest surface area by that child's two children (the
+// SAH-greedy collapse: the biggest boxes are the ones most rays enter, so they are the ones worth skipping a level for).
+// Internal children get consecutive wide-node indices from one atomic counter and go to the next level's queue.
+// Quantisation: origin = lo corner of the union, scale 2^e per axis with e the smallest exponent whose 255 steps span
+// the extent; lo planes are rounded down, hi planes up (directed-rounding subtraction), so a quantised box always
+// contains the fp32 box — the closest hit is unchanged, only a few more boxes are entered.
+// ---------------------------------------------------------------------------------------------------
+struct WideItem { int bnode, wnode; };
+struct WideCtl { uint32_t nq[RT_STACK_DEPTH + 2]; uint32_t n_wide, depth; };
+
+__global__ void k_wide_init(WideCtl* ctl, WideItem* q0) {
+    for (int i = threadIdx.x; i < RT_STACK_DEPTH + 2; i += blockDim.x) ctl->nq[i] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) { ctl->nq[0] = 1; ctl->n_wide = 1; ctl->depth = 0; q0[0] = WideItem{0, 0}; }
+}
+
+__device__ __forceinline__ void bnode_children(const BNode& b, B6 box[2], int code[2]) {
+    box[0] = B6{b.n0.x, b.n0.z, b.n2.x, b.n0.y, b.n0.w, b.n2.y};
+    box[1] = B6{b.n1.x, b.n1.z, b.n2.z, b.n1.y, b.n1.w, b.n2.w};
+    code[0] = b.child0; code[1] = b.child1;
+}
+
+__global__ void __launch_bounds__(128) k_wide_level(const BNode* __restrict__ nodes, WNode* __restrict__ wide, const WideItem* __restrict__ q_in,
+                                                    WideItem* __restrict__ q_out, WideCtl* ctl, uint32_t level) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t nq = ctl->nq[level];
+    for (uint32_t it = i; it < nq; it += gridDim.x * blockDim.x) {
+        const WideItem item = q_in[it];
+        B6 box[4];
+        int code[4];
+        int n = 2;
+        bnode_children(nodes[item.bnode], box, code);
+        if (box[1].lx > box[1].hx) n = 1;                       // the single-primitive root: its second slot is empty
+        while (n < 4) {
+            int k = -1;
+            float best = -1.f;
+            for (int c = 0; c < n; c++) if (code[c] >= 0) { const float a = b6_half_area(box[c]); if (a > best) { best = a; k = c; } }
+            if (k < 0) break;
+            B6 cb[2]; int cc[2];
+            bnode_children(nodes[code[k]], cb, cc);
+            box[k] = cb[0]; code[k] = cc[0];
+            box[n] = cb[1]; code[n] = cc[1];
+            n++;
+        }
+        B6 u = box[0];
+        for (int c = 1; c < n; c++) u = b6_unite(u, box[c]);
+        // scale 2^e per axis: the smallest power of two with 255 * 2^e >= extent (exponent bits straight from the float)
+        uint32_t eb[3];
+        float inv[3];
+        const float ext[3] = {u.hx - u.lx, u.hy - u.ly, u.hz - u.lz};
+        for (int a = 0; a < 3; a++) {
+            const float step = fmaxf(ext[a], 1e-30f) * (1.0f / 255.0f) * 1.0000002f;     // a hair more than extent / 255
+            uint32_t e = (__float_as_uint(step) >> 23) & 0xffu;
+            if (__float_as_uint(step) & 0x7fffffu) e++;                                   // round the step up to a power of two
+            e = min(max(e, 1u), 254u);
+            eb[a] = e;
+            inv[a] = __uint_as_float((254u - e) << 23);                                   // 2^-(e - 127), exact
+        }
+        uint32_t ql[3] = {0, 0, 0}, qh[3] = {0, 0, 0};
+        int cnt_internal = 0;
+        for (int c = 0; c < 4; c++) {
+            uint32_t l[3] = {255u, 255u, 255u}, h[3] = {0u, 0u, 0u};                     // empty slot: inverted box
+            if (c < n) {
+                const float lo[3] = {box[c].lx, box[c].ly, box[c].lz}, hi[3] = {box[c].hx, box[c].hy, box[c].hz}, o[3] = {u.lx, u.ly, u.lz};
+                for (int a = 0; a < 3; a++) {
+                    const float fl = floorf(__fmul_rd(__fsub_rd(lo[a], o[a]), inv[a])), fh = ceilf(__fmul_ru(__fsub_ru(hi[a], o[a]), inv[a]));
+                    l[a] = (uint32_t)fminf(fmaxf(fl, 0.f), 255.f);
+                    h[a] = (uint32_t)fminf(fmaxf(fh, 0.f), 255.f);
+                }
+                if (code[c] >= 0) cnt_internal++;
+            }
+            for (int a = 0; a < 3; a++) { ql[a] |= l[a] << (8 * c); qh[a] |= h[a] << (8 * c); }
+        }
+        uint32_t base = 0, slot = 0;
+        if (cnt_internal) { base = atomicAdd(&ctl->n_wide, (uint32_t)cnt_internal); slot = atomicAdd(&ctl->nq[level + 1], (uint32_t)cnt_internal); }
+        WNode w;
+        w.ox = u.lx; w.oy = u.ly; w.oz = u.lz;
+        w.exps = eb[0] | eb[1] << 8 | eb[2] << 16;
+        int k = 0;
+        for (int c = 0; c < 4; c++) {
+            if (c >= n) { w.child[c] = RT_WIDE_EMPTY; continue; }
+            if (code[c] >= 0) { q_out[slot + k] = WideItem{code[c], (int)(base + k)}; w.child[c] = (int)(base + k); k++; }
+            else w.child[c] = code[c];
+        }
+        w.qlo_x = ql[0]; w.qlo_y = ql[1]; w.qlo_z = ql[2]; w.qhi_x = qh[0]; w.qhi_y = qh[1]; w.qhi_z = qh[2]; w.pad0 = 0; w.pad1 = 0;
+        wide[item.wnode] = w;
+        if (it == 0) atomicMax(&ctl->depth, level + 1);
+    }
+}
+
 // bump allocator over DeviceScene::scratch; pass 1 (base == nullptr) only measures
 struct Arena {
     char* base; size_t off = 0;
@@ -1255,6 +1350,46 @@ int build_bvh_finish(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t 
     const float rx = h_ctl->root_hi[0] - h_ctl->root_lo[0], ry = h_ctl->root_hi[1] - h_ctl->root_lo[1], rz = h_ctl->root_hi[2] - h_ctl->root_lo[2];
     ds.build.sah_internal = (float)(h_ctl->area_sum / std::max(rx * ry + ry * rz + rz * rx, 1e-30f));
     ds.build.build_rounds = h_ctl->depth;
+    return RT_OK;
+}
+
+constexpr uint32_t WIDE_MIN_PRIMS = 65536;   // RT_WIDE_AUTO: scenes from this size on walk the 4-wide compressed tree
+
+int build_wide(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t stream) {
+    ds.view.wide = nullptr;
+    ds.build.n_wide_nodes = 0;
+    const uint32_t n = ds.view.n_prims;
+    if (bs.wide_nodes > RT_WIDE_ON) { set_error("commit: unknown rt_build_settings::wide_nodes"); return RT_ERR_INVALID; }
+    const bool want = bs.wide_nodes == RT_WIDE_ON || (bs.wide_nodes == RT_WIDE_AUTO && n >= WIDE_MIN_PRIMS);
+    if (!want || n == 0) return RT_OK;
+    const uint32_t n_nodes = ds.view.n_nodes;
+    RT_CUDA(ds.wide.reserve(sizeof(WNode) * (size_t)n_nodes));
+    // the collapse runs after the build's synchronisation: the build arena is free again
+    Arena measure(nullptr);
+    measure.take<WideItem>(n_nodes); measure.take<WideItem>(n_nodes); measure.take<WideCtl>(1);
+    RT_CUDA(ds.scratch.reserve(measure.off + 256));
+    Arena ar(ds.scratch.p);
+    WideItem* q[2] = {ar.take<WideItem>(n_nodes), ar.take<WideItem>(n_nodes)};
+    WideCtl* ctl = ar.take<WideCtl>(1);
+    RT_CUDA(ds.readback.reserve(sizeof(WideCtl) + 64));
+    WideCtl* h_ctl = (WideCtl*)ds.readback.p;
+    RT_CUDA(cudaEventRecord(ds.ev[6], stream));
+    k_wide_init<<<1, 128, 0, stream>>>(ctl, q[0]);
+    // a wide level consumes one to two binary levels: at most depth + 1 of them (Karras trees report no depth: the bound)
+    const uint32_t levels = ds.build.bvh_depth ? ds.build.bvh_depth + 1 : RT_STACK_DEPTH;
+    for (uint32_t l = 0; l < levels; l++) {
+        const uint32_t cap = l < 24 ? std::min<uint32_t>(1u << std::min<uint32_t>(2 * l, 30u), n_nodes) : n_nodes;   // a level holds at most 4^l nodes
+        k_wide_level<<<std::max<uint32_t>(1u, std::min<uint32_t>((cap + 127) / 128, 148u * 16u)), 128, 0, stream>>>((const BNode*)ds.nodes.p, (WNode*)ds.wide.p, q[l & 1], q[(l & 1) ^ 1], ctl, l);
+    }
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(h_ctl, ctl, sizeof(WideCtl), cudaMemcpyDeviceToHost, stream));
+    RT_CUDA(cudaEventRecord(ds.ev[7], stream));
+    RT_CUDA(cudaStreamSynchronize(stream));
+    if (h_ctl->nq[levels] != 0) { set_error("bvh build: wide collapse did not finish (internal error)"); return RT_ERR_STATE; }
+    ds.view.wide = (const WNode*)ds.wide.p;
+    ds.build.n_wide_nodes = h_ctl->n_wide;
+    ds.build.wide_depth = h_ctl->depth;
+    cudaEventElapsedTime(&ds.build.ms_wide, ds.ev[6], ds.ev[7]);
     return RT_OK;
 }
 

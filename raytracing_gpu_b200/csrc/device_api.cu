@@ -216,6 +216,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device, const rt_build_setti
     RT_CUDA(cudaStreamSynchronize(st));
     lap("synchronise");
     if ((rc = build_bvh_finish(ds, bs, st)) < 0) return rc;
+    if ((rc = build_wide(ds, bs, st)) < 0) return rc;
     if (v.n_prims) {
         cudaEvent_t* ev = ds.ev + 2;
         cudaEventElapsedTime(&ds.build.ms_morton, ev[0], ev[1]);
@@ -236,6 +237,7 @@ int commit_impl(HostScene& hs, DeviceScene& ds, int device, const rt_build_setti
     return RT_OK;
 }
 
+template <int V>
 __global__ void k_first_hit(SceneView sv, const float* rays, int n, float t_min, const float* xi, int32_t* out_id, float* out_t) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = i < n;                     // closest_hit is warp-collective: idle lanes take part in its votes
@@ -246,7 +248,7 @@ __global__ void k_first_hit(SceneView sv, const float* rays, int n, float t_min,
         r.o = make_float3(q[0], q[1], q[2]); r.d = make_float3(q[3], q[4], q[5]); r.tm = q[6];
         if (xi) x = xi[i];
     }
-    const Closest c = closest_hit<false, TV_PLAIN, 1>(sv, r, t_min, xi != nullptr, [x](uint32_t) { return x; }, nullptr, active, nullptr);
+    const Closest c = closest_hit<false, V, 1>(sv, r, t_min, xi != nullptr, [x](uint32_t) { return x; }, nullptr, active, nullptr);
     if (!active) return;
     int32_t id = -1;
     if (c.prim >= 0) id = (int32_t)sv.prim_leaf_id[c.prim];
@@ -264,6 +266,7 @@ static_assert(FHS_OFF_XI % 256 == 0 && FHS_OFF_T % 256 == 0 && FHS_OFF_ID % 256 
 static __device__ __align__(256) unsigned char g_first_hit_scratch[FHS_BYTES];   // 2.5 MiB on every GPU that loads the library, until exit
 
 // the same query as k_first_hit; device code names the array directly
+template <int V>
 __global__ void k_first_hit_static(SceneView sv, int n, float t_min, int with_xi) {
     const float* rays = reinterpret_cast<const float*>(g_first_hit_scratch);
     const float* xi = with_xi ? reinterpret_cast<const float*>(g_first_hit_scratch + FHS_OFF_XI) : nullptr;
@@ -278,7 +281,7 @@ __global__ void k_first_hit_static(SceneView sv, int n, float t_min, int with_xi
         r.o = make_float3(q[0], q[1], q[2]); r.d = make_float3(q[3], q[4], q[5]); r.tm = q[6];
         if (xi) x = xi[i];
     }
-    const Closest c = closest_hit<false, TV_PLAIN, 1>(sv, r, t_min, xi != nullptr, [x](uint32_t) { return x; }, nullptr, active, nullptr);
+    const Closest c = closest_hit<false, V, 1>(sv, r, t_min, xi != nullptr, [x](uint32_t) { return x; }, nullptr, active, nullptr);
     if (!active) return;
     int32_t id = -1;
     if (c.prim >= 0) id = (int32_t)sv.prim_leaf_id[c.prim];
@@ -375,7 +378,8 @@ extern "C" int rt_first_hit_static(rt_scene* s, const float* rays, int n, float 
     RT_CUDA(cudaMemcpyAsync(base, rays, sizeof(float) * 7 * nn, cudaMemcpyHostToDevice, st));
     if (xi) RT_CUDA(cudaMemcpyAsync(base + FHS_OFF_XI, xi, sizeof(float) * nn, cudaMemcpyHostToDevice, st));
     // nothing in the array has to start at zero: every word the kernel reads was just written, every output word below n is overwritten
-    k_first_hit_static<<<(n + 127) / 128, 128, 0, st>>>(ds->view, n, t_min, xi ? 1 : 0);
+    if (ds->view.wide) k_first_hit_static<TV_WIDE><<<(n + 127) / 128, 128, 0, st>>>(ds->view, n, t_min, xi ? 1 : 0);
+    else k_first_hit_static<TV_PLAIN><<<(n + 127) / 128, 128, 0, st>>>(ds->view, n, t_min, xi ? 1 : 0);
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(prim_id, base + FHS_OFF_ID, sizeof(int32_t) * nn, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaMemcpyAsync(t, base + FHS_OFF_T, sizeof(float) * nn, cudaMemcpyDeviceToHost, st));
@@ -400,7 +404,8 @@ extern "C" int rt_first_hit(rt_scene* s, const float* rays, int n, float t_min, 
     cudaStream_t st = ds->stream;
     RT_CUDA(cudaMemcpyAsync(d_rays, rays, sizeof(float) * 7 * nn, cudaMemcpyHostToDevice, st));
     if (xi) RT_CUDA(cudaMemcpyAsync(d_xi, xi, sizeof(float) * nn, cudaMemcpyHostToDevice, st));
-    k_first_hit<<<(n + 127) / 128, 128, 0, st>>>(ds->view, d_rays, n, t_min, d_xi, d_id, d_t);
+    if (ds->view.wide) k_first_hit<TV_WIDE><<<(n + 127) / 128, 128, 0, st>>>(ds->view, d_rays, n, t_min, d_xi, d_id, d_t);
+    else k_first_hit<TV_PLAIN><<<(n + 127) / 128, 128, 0, st>>>(ds->view, d_rays, n, t_min, d_xi, d_id, d_t);
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(prim_id, d_id, sizeof(int32_t) * nn, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaMemcpyAsync(t, d_t, sizeof(float) * nn, cudaMemcpyDeviceToHost, st));

@@ -6,6 +6,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <climits>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -45,6 +46,22 @@ struct __align__(16) BNode {
 };
 static_assert(sizeof(BNode) == 64, "BNode must be 64 bytes");
 
+// 4-wide BVH node with 8-bit child boxes (north_star (1): "wide-node SoA layout with quantised child AABBs and 128-bit
+// vectorised node loads"): 64 bytes = four 128-bit loads decide FOUR descents (BNode: two).  A child's box is
+// origin + q * 2^exp per axis, q in 0..255, rounded outwards; the planes are stored SoA (one 32-bit word holds the four
+// children's bytes of one plane), so choosing near / far planes by the sign of the ray direction is one select per axis
+// for all four children.  child >= 0: wide node index; < 0: ~primitive; RT_WIDE_EMPTY: unused slot (its box is inverted).
+// Built by collapsing the binary tree (bvh_build.cu k_wide_level); used for scenes whose binary tree outgrows the L1.
+struct __align__(16) WNode {
+    float ox, oy, oz;              // origin = lo corner of the union of the children
+    uint32_t exps;                 // biased float exponents of the three scales: ex | ey << 8 | ez << 16
+    int child[4];
+    uint32_t qlo_x, qlo_y, qlo_z, qhi_x;   // byte c of a word = child c
+    uint32_t qhi_y, qhi_z, pad0, pad1;
+};
+static_assert(sizeof(WNode) == 64, "WNode must be 64 bytes");
+#define RT_WIDE_EMPTY INT_MIN
+
 struct __align__(16) DPerlin {
     float4 ranvec[256];   // xyz used
     uint8_t perm[3][256];
@@ -70,6 +87,7 @@ struct SceneView {
     const DPerlin* perlins;
     const DImage* images;
     const BNode* nodes;            // nodes[0] = root (n_prims >= 1)
+    const WNode* wide;             // non-null: the traversal walks the 4-wide compressed tree instead (wide[0] = root)
     uint32_t n_prims, n_media, n_nodes, n_active_media;
     rt_flat_camera camera;
     float background[3];
@@ -148,6 +166,9 @@ int build_bvh(DeviceScene& ds, const rt_build_settings& bs, const DPrim* d_prims
 // bvh_build.cu: after the commit's one synchronisation — reads the build's control block, fills the statistics, and rebuilds
 // with PLOC in the one case the sweep gives up on (a degenerate chain deeper than RT_STACK_DEPTH)
 int build_bvh_finish(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t stream);
+// bvh_build.cu: collapses the finished binary tree into ds.wide (4-wide, 8-bit boxes) where the settings / scene size ask
+// for it; synchronises the stream once more.  Sets ds.view.wide and ds.build.n_wide_nodes.
+int build_wide(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t stream);
 
 // bvh_build.cu: fills DMedium::lo / hi of every medium (in place, device)
 int compute_medium_bounds(DeviceScene& ds, DMedium* media, float time_lo, float time_hi, cudaStream_t stream);

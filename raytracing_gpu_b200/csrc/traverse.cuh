@@ -18,6 +18,8 @@ struct Closest {
 
 struct TraversalCounters { uint32_t nodes, prim_tests; };
 
+#define RT_NODE_DONE INT_MIN   // "no node": a finished lane, an empty stack, an empty slot of a wide node
+
 // ties: the reference's hittable_list lets the LATER object win (t == closest_so_far is accepted,
 // sphere.h:49, aarect.h:66) — with an unordered traversal that becomes "higher leaf id wins".
 __device__ __forceinline__ void consider(const SceneView& sv, int prim, float t, Closest& best) {
@@ -80,6 +82,45 @@ __device__ __forceinline__ NodeHit node_step(const BNode* np, const SlabRay& s, 
     return r;
 }
 
+// ---- the wide node step (WNode: four children, 8-bit boxes) ---------------------------------------------------------------
+// Per node: three scales 2^e and the three offsets (origin - ray origin) / d, then per child and axis one byte -> float
+// (PRMT into the mantissa of 2^23, minus 2^23: exact) and one FMA per plane.  Near / far planes are chosen for all four
+// children at once by swapping the packed lo / hi words of an axis when the direction is negative.  The four candidates
+// are sorted by entry distance (misses last) with a five-comparator network.
+struct WideHits { float t[4]; int c[4]; };   // ascending entry distance; a miss is (+inf, RT_NODE_DONE)
+__device__ __forceinline__ float byte_to_float(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f; }
+__device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s, float t_min, float t_max) {
+    const uint4 w0 = __ldg(reinterpret_cast<const uint4*>(np)), w1 = __ldg(reinterpret_cast<const uint4*>(np) + 1);
+    const uint4 w2 = __ldg(reinterpret_cast<const uint4*>(np) + 2), w3 = __ldg(reinterpret_cast<const uint4*>(np) + 3);
+    const float ix = s.ax + s.bx, iy = s.ay + s.by, iz = s.az + s.bz;                 // one of each pair is zero: exact
+    const float sx = __uint_as_float((w0.w & 0xffu) << 23) * ix, sy = __uint_as_float(((w0.w >> 8) & 0xffu) << 23) * iy,
+                sz = __uint_as_float(((w0.w >> 16) & 0xffu) << 23) * iz;
+    const float bx = fmaf(__uint_as_float(w0.x), ix, -s.ox), by = fmaf(__uint_as_float(w0.y), iy, -s.oy), bz = fmaf(__uint_as_float(w0.z), iz, -s.oz);
+    const bool px = ix >= 0.f, py = iy >= 0.f, pz = iz >= 0.f;
+    const uint32_t nx = px ? w2.x : w2.w, fx = px ? w2.w : w2.x;                      // qlo_x / qhi_x
+    const uint32_t ny = py ? w2.y : w3.x, fy = py ? w3.x : w2.y;                      // qlo_y / qhi_y
+    const uint32_t nz = pz ? w2.z : w3.y, fz = pz ? w3.y : w2.z;                      // qlo_z / qhi_z
+    const int code[4] = {(int)w1.x, (int)w1.y, (int)w1.z, (int)w1.w};
+    WideHits h;
+    #pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint32_t sel = 0x7540u | (uint32_t)c;
+        const float tn = fmaxf(fmaxf(fmaf(byte_to_float(nx, sel), sx, bx), fmaf(byte_to_float(ny, sel), sy, by)), fmaxf(fmaf(byte_to_float(nz, sel), sz, bz), t_min));
+        const float tf = fminf(fminf(fmaf(byte_to_float(fx, sel), sx, bx), fmaf(byte_to_float(fy, sel), sy, by)), fminf(fmaf(byte_to_float(fz, sel), sz, bz), t_max));
+        const bool hit = tn <= tf && code[c] != RT_WIDE_EMPTY;
+        h.t[c] = hit ? tn : INFINITY;
+        h.c[c] = hit ? code[c] : RT_NODE_DONE;
+    }
+    auto cswap = [&](int a, int b) {
+        const bool sw = h.t[b] < h.t[a];
+        const float ta = sw ? h.t[b] : h.t[a], tb = sw ? h.t[a] : h.t[b];
+        const int ca = sw ? h.c[b] : h.c[a], cb = sw ? h.c[a] : h.c[b];
+        h.t[a] = ta; h.t[b] = tb; h.c[a] = ca; h.c[b] = cb;
+    };
+    cswap(0, 1); cswap(2, 3); cswap(0, 2); cswap(1, 3); cswap(1, 2);
+    return h;
+}
+
 // ---- the traversal stack --------------------------------------------------------------------------------------------
 // Variants (template bit mask V), each measured against the plain one on the same box (profiles/r02_*):
 //   TV_TCULL  an entry carries the distance at which the ray enters the pushed box; a pop discards entries that the
@@ -91,9 +132,10 @@ __device__ __forceinline__ NodeHit node_step(const BNode* np, const SlabRay& s, 
 //             trees no deeper than that (a stack never holds more entries than the tree has levels); deeper trees walk
 //             with the local-memory stack.
 //   TV_MINMAX min / max plane selection on the ALU pipe, as in round 1
-#define RT_NODE_DONE INT_MIN
+//   TV_WIDE   the 4-wide compressed tree: a step sorts up to four entered children, descends into the nearest and pushes
+//             the rest far-to-near (RT_NODE_DONE is INT_MIN = RT_WIDE_EMPTY: "no node" in both encodings)
 #define RT_SHORT_STACK 16
-enum : int { TV_PLAIN = 0, TV_TCULL = 1, TV_SMEM = 2, TV_MINMAX = 4 };
+enum : int { TV_PLAIN = 0, TV_TCULL = 1, TV_SMEM = 2, TV_MINMAX = 4, TV_WIDE = 8 /* walks SceneView::wide (4-wide, 8-bit boxes); plain stack only */ };
 
 // Closest surface hit.  A lane that reaches a leaf parks it (one register) and keeps walking; the warp enters the leaf code
 // only when some lane reaches a second leaf or nobody has nodes left, then every parked leaf is tested together (round 1:
@@ -137,15 +179,24 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     int parked = RT_NODE_DONE;
     for (;;) {
         if (node >= 0) {
-            const NodeHit h = node_step<V>(sv.nodes + node, s, t_min, best.t);
-            if (COUNT) cnt->nodes++;
-            if (h.h0 && h.h1) {
-                const bool swap = h.t1n < h.t0n;
-                push(swap ? h.c0 : h.c1, swap ? h.t0n : h.t1n);
-                node = swap ? h.c1 : h.c0;
-            } else if (h.h0) node = h.c0;
-            else if (h.h1) node = h.c1;
-            else node = pop(best.t);
+            if constexpr ((V & TV_WIDE) != 0) {
+                const WideHits h = wide_step(sv.wide + node, s, t_min, best.t);
+                if (COUNT) cnt->nodes++;
+                if (h.c[3] != RT_NODE_DONE) push(h.c[3], h.t[3]);
+                if (h.c[2] != RT_NODE_DONE) push(h.c[2], h.t[2]);
+                if (h.c[1] != RT_NODE_DONE) push(h.c[1], h.t[1]);
+                node = h.c[0] != RT_NODE_DONE ? h.c[0] : pop(best.t);
+            } else {
+                const NodeHit h = node_step<V>(sv.nodes + node, s, t_min, best.t);
+                if (COUNT) cnt->nodes++;
+                if (h.h0 && h.h1) {
+                    const bool swap = h.t1n < h.t0n;
+                    push(swap ? h.c0 : h.c1, swap ? h.t0n : h.t1n);
+                    node = swap ? h.c1 : h.c0;
+                } else if (h.h0) node = h.c0;
+                else if (h.h1) node = h.c1;
+                else node = pop(best.t);
+            }
             if (node < 0 && node != RT_NODE_DONE && parked == RT_NODE_DONE) { parked = node; node = pop(best.t); }
         }
         const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
@@ -181,7 +232,7 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
 #define RT_SUSPEND_STACK 24
 struct Walk { int node, parked, sp; };
 
-template <bool COUNT>
+template <bool COUNT, bool WIDE>
 __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray& ray, float t_min, Closest& best, TraversalCounters* cnt,
                                                  Walk& w, int* stack, uint32_t suspend_below, uint32_t* steps) {
     const SlabRay s = slab_ray(ray);
@@ -191,15 +242,24 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
     auto pop = [&]() { return sp ? stack[--sp] : RT_NODE_DONE; };
     for (;;) {
         if (node >= 0) {
-            const NodeHit h = node_step<0>(sv.nodes + node, s, t_min, best.t);
-            if (COUNT) cnt->nodes++;
-            if (h.h0 && h.h1) {
-                const bool swap = h.t1n < h.t0n;
-                stack[sp++] = swap ? h.c0 : h.c1;
-                node = swap ? h.c1 : h.c0;
-            } else if (h.h0) node = h.c0;
-            else if (h.h1) node = h.c1;
-            else node = pop();
+            if constexpr (WIDE) {
+                const WideHits h = wide_step(sv.wide + node, s, t_min, best.t);
+                if (COUNT) cnt->nodes++;
+                if (h.c[3] != RT_NODE_DONE) stack[sp++] = h.c[3];
+                if (h.c[2] != RT_NODE_DONE) stack[sp++] = h.c[2];
+                if (h.c[1] != RT_NODE_DONE) stack[sp++] = h.c[1];
+                node = h.c[0] != RT_NODE_DONE ? h.c[0] : pop();
+            } else {
+                const NodeHit h = node_step<0>(sv.nodes + node, s, t_min, best.t);
+                if (COUNT) cnt->nodes++;
+                if (h.h0 && h.h1) {
+                    const bool swap = h.t1n < h.t0n;
+                    stack[sp++] = swap ? h.c0 : h.c1;
+                    node = swap ? h.c1 : h.c0;
+                } else if (h.h0) node = h.c0;
+                else if (h.h1) node = h.c1;
+                else node = pop();
+            }
             if (node < 0 && node != RT_NODE_DONE && parked == RT_NODE_DONE) { parked = node; node = pop(); }
         }
         const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked

@@ -262,10 +262,10 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
 // suspended path simply bounces an iteration later.  Nothing waits for stragglers: a second pass inside the same
 // iteration raised the lane utilisation of the node loop just as much but paid for it with the latency of the longest
 // walks at the end of every iteration (profiles/r01_v9_experiments.md).
-template <bool COUNT>
 #ifndef DEFER_MIN_BLOCKS
 #define DEFER_MIN_BLOCKS EXTEND_MIN_BLOCKS
 #endif
+template <bool COUNT, bool WIDE>
 __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer(SceneView sv, PoolView pv, FrameParams fp, int cur, uint32_t suspend_below) {
     const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
     const int rd = cur ^ 1, wr = cur;
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
         Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
         // only whole batches suspend: a few stragglers left over at the end of a list would otherwise advance a leaf phase per iteration
         const uint32_t below = __all_sync(0xffffffffu, active) ? suspend_below : 0u;
-        walk_suspendable<COUNT>(sv, r, 0.001f, c, &tc, w, stack, below, &steps);                                    // render.h:63
+        walk_suspendable<COUNT, WIDE>(sv, r, 0.001f, c, &tc, w, stack, below, &steps);                                    // render.h:63
         const bool suspended = w.node != RT_NODE_DONE || w.parked != RT_NODE_DONE;
         const uint32_t ms = __ballot_sync(0xffffffffu, suspended);
         if (ms) {
@@ -669,6 +669,7 @@ uint32_t suspend_threshold(const DeviceScene& ds, const rt_render_settings& st) 
 
 // traversal variant of k_extend: the caller's, else the default; the shared-memory stack only for trees it can hold
 int extend_variant(const DeviceScene& ds, const rt_render_settings& st) {
+    if (ds.view.wide) return TV_WIDE;   // the committed scene carries the 4-wide compressed tree: one variant walks it
     int v = (st.traversal & RT_TRAVERSAL_FORCE) ? (int)(st.traversal & 7u) : (int)RT_TRAVERSAL_DEFAULT_BITS;
     if (ds.build.bvh_depth == 0 || ds.build.bvh_depth + 1 > RT_SHORT_STACK) v &= ~TV_SMEM;
     return v;
@@ -683,7 +684,8 @@ template <bool COUNT> void launch_extend(int v, int grid, cudaStream_t s, const 
     case 4: k_extend<COUNT, 4><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 5: k_extend<COUNT, 5><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 6: k_extend<COUNT, 6><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
-    default: k_extend<COUNT, 7><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 7: k_extend<COUNT, 7><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    default: k_extend<COUNT, TV_WIDE><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     }
 }
 int extend_occupancy(int v, int* occ) {
@@ -695,7 +697,8 @@ int extend_occupancy(int v, int* occ) {
     case 4: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 4>, EXTEND_BLOCK, 0)); break;
     case 5: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 5>, EXTEND_BLOCK, 0)); break;
     case 6: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 6>, EXTEND_BLOCK, 0)); break;
-    default: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 7>, EXTEND_BLOCK, 0)); break;
+    case 7: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 7>, EXTEND_BLOCK, 0)); break;
+    default: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, TV_WIDE>, EXTEND_BLOCK, 0)); break;
     }
     return RT_OK;
 }
@@ -731,7 +734,7 @@ int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
             RT_CUDA(cudaMalloc(&p->v.cont_sp[b], sizeof(uint8_t) * capacity));
             RT_CUDA(cudaMalloc(&p->v.cont_stack[b], sizeof(int) * (size_t)capacity * RT_SUSPEND_STACK));
         }
-        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend_defer<false>, EXTEND_BLOCK, 0));
+        RT_CUDA((cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend_defer<false, false>, EXTEND_BLOCK, 0)));
         p->grid_extend = sms * std::max(occ, 1);
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_defer, SHADE_BLOCK, 0));
         p->grid_shade = sms * std::max(occ, 1);
@@ -820,8 +823,11 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     auto launch_iteration = [&](int cur, uint32_t slot, cudaStream_t s, bool timed) -> int {
         if (timed && tick() < 0) return RT_ERR_CUDA;
         if (P.suspend_below) {
-            if (count) k_extend_defer<true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
-            else k_extend_defer<false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
+            if (ds.view.wide) {
+                if (count) k_extend_defer<true, true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
+                else k_extend_defer<false, true><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
+            } else if (count) k_extend_defer<true, false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
+            else k_extend_defer<false, false><<<P.grid_extend, EXTEND_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, P.suspend_below);
         } else if (count) launch_extend<true>(variant, P.grid_extend, s, ds.view, P.v, fp, cur);
         else launch_extend<false>(variant, P.grid_extend, s, ds.view, P.v, fp, cur);
         if (timed && tick() < 0) return RT_ERR_CUDA;

@@ -21,7 +21,8 @@ reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 scene, width, aspect, _, desc = WORKLOADS[name]
 height = image_height(width, aspect)
 sc, _ = bench.build_scene(rt, scene, aspect)
-st = sc.commit(0)
+wide = {"on": rt.capi.WIDE_ON, "off": rt.capi.WIDE_OFF}.get(os.environ.get("AB_WIDE", ""), rt.capi.WIDE_AUTO)
+st = sc.commit(0, wide_nodes=wide)
 dev = torch.device("cuda", 0)
 accum = torch.zeros(height, width, 3, device=dev)
 stream = torch.cuda.current_stream().cuda_stream
@@ -47,9 +48,10 @@ def run(label, **kw):
 
 
 print(json.dumps({"workload": desc, "prims": st.n_prims, "builder": st.builder, "bvh_depth": st.bvh_depth, "sah": st.sah_internal,
-                  "build_ms": st.ms_total, "host_ms": st.ms_host}), flush=True)
+                  "build_ms": st.ms_total, "host_ms": st.ms_host, "n_nodes": st.n_nodes, "n_wide_nodes": st.n_wide_nodes, "wide_depth": st.wide_depth,
+                  "ms_wide": st.ms_wide}), flush=True)
 deferred = st.n_prims >= 65536
-tag = os.path.basename(rt.lib_path())
+tag = os.path.basename(rt.lib_path()) + (" wide" if st.n_wide_nodes else " binary")
 run(f"default [{tag}]")
 run("warp_shade", debug_flags=rt.capi.DEBUG_WARP_SHADE)
 if os.environ.get("AB_ONLY_DEFAULT"):
