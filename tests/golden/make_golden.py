@@ -39,6 +39,25 @@ def build(L, name):
     return L.ref_scene_named(name.encode())
 
 
+# second set: converged reference renders at 256 pixels wide for the per-channel RMSE / PSNR test (float16 keeps the
+# fixtures small; its 5e-4 relative rounding is far below the Monte-Carlo noise at these sample counts)
+WIDE_IMAGES = {"final": (256, 1024), "cornell_smoke": (256, 1024), "big1": (256, 512)}
+
+
+def main_wide():
+    L = helpers.ref_lib()
+    assert L is not None, "build oracle/_ref first"
+    threads = os.cpu_count() or 1
+    for name, (w, spp) in WIDE_IMAGES.items():
+        t0 = time.time()
+        h = build(L, name)
+        hgt = L.ref_image_height(h, w)
+        fb = np.zeros((hgt, w, 3), np.float32)
+        L.ref_render(h, w, hgt, spp, 50, 0, threads, fb.ctypes.data)
+        np.savez_compressed(os.path.join(helpers.GOLDEN, name + "_256.npz"), image=fb.astype(np.float16), image_spp=np.int32(spp))
+        print(f"{name}_256: {w}x{hgt}@{spp} mean={fb.mean():.4f} max={fb.max():.2f} ({time.time() - t0:.1f}s)")
+
+
 def main():
     L = helpers.ref_lib()
     assert L is not None, "build oracle/_ref first"
@@ -68,4 +87,8 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--wide" in sys.argv:
+        main_wide()        # only the 256-pixel images (the first set is not regenerated)
+    else:
+        main()
+        main_wide()

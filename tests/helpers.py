@@ -184,6 +184,19 @@ def rmse(a, b):
 from workloads import procedural_image, procedural_mesh, MESH_CAMERA  # noqa: E402,F401  (synthetic inputs shared with bench.py)
 
 
+def channel_rmse(a, b):
+    """Per-channel RMSE of two (H, W, 3) images."""
+    d = np.asarray(a, np.float64) - np.asarray(b, np.float64)
+    return np.sqrt((d * d).mean(axis=(0, 1)))
+
+
+def channel_psnr(a, b, peak=1.0):
+    """Per-channel PSNR in dB of two linear-radiance images clipped to [0, peak] (what an 8-bit output stage would show)."""
+    d = np.clip(np.asarray(a, np.float64), 0, peak) - np.clip(np.asarray(b, np.float64), 0, peak)
+    mse = (d * d).mean(axis=(0, 1))
+    return 10.0 * np.log10(peak * peak / np.maximum(mse, 1e-20))
+
+
 def media_leaf_ids(blob):
     """Leaf ids of the constant_medium objects in an export blob (layout: include/rt_flat.h)."""
     h = blob_header(blob)
