@@ -11,7 +11,7 @@
  * create_*_world kernels and in the same order as oracle/ref_harness.cpp::build_final.
  *
  * usage: ref_cuda <big1|cornell_smoke|cornell|final> <width> <spp> <max_depth> [earth.rgb8 w h] [image_out.f32]
- *        ref_cuda <scene> probe <rays.f32 (n x 7)> <out.f32 (n t values, then n x 3 normals)> [earth.rgb8 w h]
+ *        ref_cuda <scene> probe <rays.f32 (n x 7)> <out (n float t, n x 3 float normals, n int32 leaf ids)> [earth.rgb8 w h]
  * prints one JSON line.  Only bench.py's reference legs and tests/ may execute it.
  * Everything in this file is harness code written for this repo; no reference code is copied.
  */
@@ -95,10 +95,76 @@ struct final_scene : public scene {
     }
 };
 
+/* ---- leaf ids on the device (same DFS order as the product's flattener and as oracle/ref_harness.cpp's tagger) ------------
+ * Device code has no RTTI; the dynamic type of an object is read from its vtable pointer, compared with the vtable pointer
+ * of one exemplar per class constructed in the same kernel.  Every leaf's material is wrapped in a tag_material that
+ * carries the leaf id and forwards scatter / emitted, so rendering is unchanged; the probe reads the id back from
+ * rec.mat_ptr.  Boundary leaves of a constant_medium consume ids but never report (the medium's phase function does). */
+struct tag_material : public material {
+    material* real;
+    int leaf_id;
+    __device__ tag_material(material* r, int id) : real(r), leaf_id(id) {}
+    __device__ bool scatter(const ray& ray_in, const hit_record& rec, color& attenuation, ray& scattered, curandState* s) const override {
+        return real->scatter(ray_in, rec, attenuation, scattered, s);
+    }
+    __device__ color emitted(const float u, const float v, const point3& p) const override { return real->emitted(u, v, p); }
+};
+struct vtables { void *sphere_, *moving_sphere_, *xy_, *xz_, *yz_, *box_, *translate_, *rotate_y_, *medium_, *list_, *bvh_, *tag_; };
+__device__ inline void* vptr_of(const void* obj) { return *(void* const*)obj; }
+
+__device__ material* tag_wrap(material* m, bool visible, int& next, const vtables& vt) {
+    const int id = next++;
+    if (!visible || vptr_of(m) == vt.tag_) return m;
+    return new tag_material(m, id);
+}
+__device__ void tag_walk(hittable* h, bool visible, int& next, const vtables& vt, int* unknown) {
+    void* v = vptr_of(h);
+    if (v == vt.sphere_) { sphere* p = (sphere*)h; p->mat_ptr = tag_wrap(p->mat_ptr, visible, next, vt); return; }
+    if (v == vt.moving_sphere_) { moving_sphere* p = (moving_sphere*)h; p->mat_ptr = tag_wrap(p->mat_ptr, visible, next, vt); return; }
+    if (v == vt.xy_) { xy_rect* p = (xy_rect*)h; p->mp = tag_wrap(p->mp, visible, next, vt); return; }
+    if (v == vt.xz_) { xz_rect* p = (xz_rect*)h; p->mp = tag_wrap(p->mp, visible, next, vt); return; }
+    if (v == vt.yz_) { yz_rect* p = (yz_rect*)h; p->mp = tag_wrap(p->mp, visible, next, vt); return; }
+    if (v == vt.box_) { box* p = (box*)h; for (int i = 0; i < 6; i++) tag_walk(p->temp_hittable[i], visible, next, vt, unknown); return; }
+    if (v == vt.translate_) { tag_walk(((translate*)h)->ptr, visible, next, vt, unknown); return; }
+    if (v == vt.rotate_y_) { tag_walk(((rotate_y*)h)->ptr, visible, next, vt, unknown); return; }
+    if (v == vt.medium_) {
+        constant_medium* p = (constant_medium*)h;
+        p->phase_function = tag_wrap(p->phase_function, visible, next, vt);
+        tag_walk(p->boundary, false, next, vt, unknown);
+        return;
+    }
+    if (v == vt.list_) { hittable_list* p = (hittable_list*)h; for (int i = 0; i < p->list_size; i++) tag_walk(p->objects[i], visible, next, vt, unknown); return; }
+    if (v == vt.bvh_) { bvh_node* p = (bvh_node*)h; for (int i = 0; i < p->n; i++) tag_walk(p->objs[i], visible, next, vt, unknown); return; }
+    atomicAdd(unknown, 1);
+}
+__global__ void tag_world(hittable** world, vtables* out_vt, int* out_counts /* leaves, unknown */) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    curandState rs;
+    curand_init(1, 0, 0, &rs);
+    material* m = new lambertian(color(0, 0, 0));
+    hittable** two = new hittable*[2];
+    two[0] = new sphere(point3(0, 0, 0), 1, m); two[1] = new sphere(point3(3, 0, 0), 1, m);
+    vtables vt;
+    vt.sphere_ = vptr_of(two[0]);
+    vt.moving_sphere_ = vptr_of(new moving_sphere(point3(0, 0, 0), point3(1, 0, 0), 0, 1, 1, m));
+    vt.xy_ = vptr_of(new xy_rect(0, 1, 0, 1, 0, m)); vt.xz_ = vptr_of(new xz_rect(0, 1, 0, 1, 0, m)); vt.yz_ = vptr_of(new yz_rect(0, 1, 0, 1, 0, m));
+    vt.box_ = vptr_of(new box(point3(0, 0, 0), point3(1, 1, 1), m));
+    vt.translate_ = vptr_of(new translate(two[0], vec3(0, 0, 0)));
+    vt.rotate_y_ = vptr_of(new rotate_y(two[0], 0));
+    vt.medium_ = vptr_of(new constant_medium(two[0], 1.0f, color(1, 1, 1)));
+    vt.list_ = vptr_of(new hittable_list(two, 2));
+    vt.bvh_ = vptr_of(new bvh_node());   // (the default constructor: only the vtable pointer is read)
+    vt.tag_ = vptr_of(new tag_material(m, -1));
+    int next = 0, unknown = 0;
+    tag_walk(*world, true, next, vt, &unknown);
+    *out_vt = vt;
+    out_counts[0] = next; out_counts[1] = unknown;
+}
+
 /* Route-B probe: the reference's own device intersection code asked for the closest hit of caller-supplied
  * rays, exactly as color_f does at render.h:63.  One thread per ray; t = +inf on a miss.  constant_medium draws from the
  * per-thread cuRAND state, so media hits are stochastic: compare those scenes on surface hits only. */
-__global__ void probe_first_hit(hittable** world, const float* rays, int n, float* out_t, float* out_normal) {
+__global__ void probe_first_hit(hittable** world, const float* rays, int n, float* out_t, float* out_normal, int* out_id, const vtables* vt) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     curandState rs;
@@ -108,6 +174,7 @@ __global__ void probe_first_hit(hittable** world, const float* rays, int n, floa
     hit_record rec;
     const bool hit = (*world)->hit(r, 0.001f, infinity, rec, &rs);
     out_t[i] = hit ? rec.t : infinity;
+    out_id[i] = (hit && vt && vptr_of(rec.mat_ptr) == vt->tag_) ? ((const tag_material*)rec.mat_ptr)->leaf_id : -1;
     out_normal[3 * i] = hit ? rec.normal.x() : 0.f; out_normal[3 * i + 1] = hit ? rec.normal.y() : 0.f; out_normal[3 * i + 2] = hit ? rec.normal.z() : 0.f;
 }
 
@@ -117,6 +184,7 @@ static int run_probe(scene* sc, const char* rays_path, const char* out_path) {
     fseek(f, 0, SEEK_END); const long bytes = ftell(f); fseek(f, 0, SEEK_SET);
     const int n = (int)(bytes / (7 * sizeof(float)));
     std::vector<float> rays((size_t)n * 7), t(n), nrm((size_t)n * 3);
+    std::vector<int> ids(n);
     if (fread(rays.data(), sizeof(float), rays.size(), f) != rays.size()) { fclose(f); return 2; }
     fclose(f);
     float *d_rays, *d_t, *d_n;
@@ -124,7 +192,15 @@ static int run_probe(scene* sc, const char* rays_path, const char* out_path) {
     checkCudaErrors(cudaMalloc((void**)&d_t, n * sizeof(float)));
     checkCudaErrors(cudaMalloc((void**)&d_n, 3 * (size_t)n * sizeof(float)));
     checkCudaErrors(cudaMemcpy(d_rays, rays.data(), rays.size() * sizeof(float), cudaMemcpyHostToDevice));
-    probe_first_hit<<<(n + 63) / 64, 64>>>(sc->d_world, d_rays, n, d_t, d_n);
+    vtables* d_vt; int *d_counts, *d_id, counts[2] = {0, 0};
+    checkCudaErrors(cudaMalloc((void**)&d_vt, sizeof(vtables)));
+    checkCudaErrors(cudaMalloc((void**)&d_counts, 2 * sizeof(int)));
+    checkCudaErrors(cudaMalloc((void**)&d_id, n * sizeof(int)));
+    tag_world<<<1, 1>>>(sc->d_world, d_vt, d_counts);
+    checkCudaErrors(cudaGetLastError());
+    checkCudaErrors(cudaDeviceSynchronize());
+    checkCudaErrors(cudaMemcpy(counts, d_counts, sizeof(counts), cudaMemcpyDeviceToHost));
+    probe_first_hit<<<(n + 63) / 64, 64>>>(sc->d_world, d_rays, n, d_t, d_n, d_id, d_vt);
     checkCudaErrors(cudaGetLastError());
     checkCudaErrors(cudaDeviceSynchronize());
     checkCudaErrors(cudaMemcpy(t.data(), d_t, n * sizeof(float), cudaMemcpyDeviceToHost));
@@ -133,8 +209,10 @@ static int run_probe(scene* sc, const char* rays_path, const char* out_path) {
     if (!f) return 2;
     fwrite(t.data(), sizeof(float), t.size(), f);
     fwrite(nrm.data(), sizeof(float), nrm.size(), f);
+    checkCudaErrors(cudaMemcpy(ids.data(), d_id, n * sizeof(int), cudaMemcpyDeviceToHost));
+    fwrite(ids.data(), sizeof(int), ids.size(), f);
     fclose(f);
-    printf("{\"impl\": \"reference_cuda\", \"mode\": \"probe\", \"rays\": %d}\n", n);
+    printf("{\"impl\": \"reference_cuda\", \"mode\": \"probe\", \"rays\": %d, \"leaves\": %d, \"unknown_types\": %d}\n", n, counts[0], counts[1]);
     return 0;
 }
 

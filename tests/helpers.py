@@ -217,10 +217,11 @@ def assert_first_hit_parity(blob, ids, t, want_ids, want_t):
         np.testing.assert_allclose(t[med], want_t[med], rtol=1e-6, atol=0)
 
 
-def ref_cuda_probe(scene_name, rays, image=None, exe="ref_cuda_nofma"):
+def ref_cuda_probe(scene_name, rays, image=None, exe="ref_cuda_nofma", with_ids=False):
     """First-hit distances from the REFERENCE's own device code: oracle/_ref/<exe> builds the named scene with the
     reference's kernels and runs world->hit (hittable_list.h / bvh.h) on `rays` in one CUDA thread per ray.  Returns
-    float32 t (inf = miss), or None when the binary was not built (it is compiled from /root/reference by
+    float32 t (inf = miss) — with_ids: (t, int32 DFS leaf ids read back from the materials the harness tagged on the device, info) —
+    or None when the binary was not built (it is compiled from /root/reference by
     oracle/Makefile in the authoring container and travels to the GPU box)."""
     import subprocess
     import tempfile
@@ -235,6 +236,10 @@ def ref_cuda_probe(scene_name, rays, image=None, exe="ref_cuda_nofma"):
             ip = os.path.join(d, "image.rgb8")
             np.ascontiguousarray(image, np.uint8).tofile(ip)
             extra = [ip, str(image.shape[1]), str(image.shape[0])]
-        subprocess.check_call([path, scene_name, "probe", rp, op] + extra, stdout=subprocess.DEVNULL)
+        res = subprocess.run([path, scene_name, "probe", rp, op] + extra, check=True, capture_output=True, text=True)
         out = np.fromfile(op, np.float32)
-    return out[:len(rays)]
+    n = len(rays)
+    if not with_ids:
+        return out[:n]
+    import json
+    return out[:n], out[4 * n:5 * n].view(np.int32), json.loads(res.stdout.strip().splitlines()[-1])
