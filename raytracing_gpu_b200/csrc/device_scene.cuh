@@ -61,9 +61,6 @@ struct __align__(16) WNode {
 };
 static_assert(sizeof(WNode) == 64, "WNode must be 64 bytes");
 #define RT_WIDE_EMPTY INT_MIN
-#ifndef RT_WIDE_MAGIC
-#define RT_WIDE_MAGIC 0   // see traverse.cuh (builder and traversal must agree)
-#endif
 
 struct __align__(16) DPerlin {
     float4 ranvec[256];   // xyz used

@@ -86,31 +86,18 @@ __device__ __forceinline__ NodeHit node_step(const BNode* np, const SlabRay& s, 
 // Per node: three scales 2^e and the three offsets (origin - ray origin) / d, then per child and axis one byte -> float
 // (PRMT into the mantissa of 2^23, minus 2^23: exact) and one FMA per plane.  Near / far planes are chosen for all four
 // children at once by swapping the packed lo / hi words of an axis when the direction is negative.  The four candidates
-// are sorted by entry distance (misses last) with a five-comparator network.
+// are sorted by entry distance (misses last) with a five-comparator network.  Measured and not adopted on the 1 M-triangle
+// mesh (profiles/r02_wide_nodes.md): folding the 2^23 into the plane offset (saves 24 FADD, but the builder must pad every box
+// by a quantisation step: +7 % node visits, extend +1.8 %), and sorting only the nearest child to the front (+1 % visits, +0.8 %).
 struct WideHits { float t[4]; int c[4]; };   // ascending entry distance; a miss is (+inf, RT_NODE_DONE)
-#ifndef RT_WIDE_MAGIC
-#define RT_WIDE_MAGIC 0     // 1: fold the 2^23 of the byte -> float trick into the plane offset (one FADD less per plane; the builder
-#endif                      //    then pads every child box by one quantisation step, which covers the half step this rounding can move it)
-#ifndef RT_WIDE_SORT
-#define RT_WIDE_SORT 1      // 1: the entered children are fully sorted by distance; 0: nearest first, the others pushed as they come
-#endif
-#if RT_WIDE_MAGIC
-__device__ __forceinline__ float byte_to_float(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)); }   // 2^23 + byte
-#else
 __device__ __forceinline__ float byte_to_float(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f; }
-#endif
 __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s, float t_min, float t_max) {
     const uint4 w0 = __ldg(reinterpret_cast<const uint4*>(np)), w1 = __ldg(reinterpret_cast<const uint4*>(np) + 1);
     const uint4 w2 = __ldg(reinterpret_cast<const uint4*>(np) + 2), w3 = __ldg(reinterpret_cast<const uint4*>(np) + 3);
     const float ix = s.ax + s.bx, iy = s.ay + s.by, iz = s.az + s.bz;                 // one of each pair is zero: exact
     const float sx = __uint_as_float((w0.w & 0xffu) << 23) * ix, sy = __uint_as_float(((w0.w >> 8) & 0xffu) << 23) * iy,
                 sz = __uint_as_float(((w0.w >> 16) & 0xffu) << 23) * iz;
-#if RT_WIDE_MAGIC
-    const float bx = fmaf(-8388608.0f, sx, fmaf(__uint_as_float(w0.x), ix, -s.ox)), by = fmaf(-8388608.0f, sy, fmaf(__uint_as_float(w0.y), iy, -s.oy)),
-                bz = fmaf(-8388608.0f, sz, fmaf(__uint_as_float(w0.z), iz, -s.oz));
-#else
     const float bx = fmaf(__uint_as_float(w0.x), ix, -s.ox), by = fmaf(__uint_as_float(w0.y), iy, -s.oy), bz = fmaf(__uint_as_float(w0.z), iz, -s.oz);
-#endif
     const bool px = ix >= 0.f, py = iy >= 0.f, pz = iz >= 0.f;
     const uint32_t nx = px ? w2.x : w2.w, fx = px ? w2.w : w2.x;                      // qlo_x / qhi_x
     const uint32_t ny = py ? w2.y : w3.x, fy = py ? w3.x : w2.y;                      // qlo_y / qhi_y
@@ -132,11 +119,7 @@ __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s,
         const int ca = sw ? h.c[b] : h.c[a], cb = sw ? h.c[a] : h.c[b];
         h.t[a] = ta; h.t[b] = tb; h.c[a] = ca; h.c[b] = cb;
     };
-#if RT_WIDE_SORT
     cswap(0, 1); cswap(2, 3); cswap(0, 2); cswap(1, 3); cswap(1, 2);
-#else
-    cswap(0, 1); cswap(2, 3); cswap(0, 2);          // slot 0 = the nearest; misses may sit between hits: callers test every slot
-#endif
     return h;
 }
 
