@@ -153,6 +153,33 @@ static scene* build_final(const unsigned char* img, int w, int h, int bpp, float
     return s;
 }
 
+/* A composition for the media-ordering edge cases: two OVERLAPPING box-bounded media, a medium listed BEFORE a
+ * surface that lies in front of its far side, and a medium listed before a NEARER medium — in a hittable_list a medium
+ * only sees the objects listed before it and shrinks t_max for the ones after it (hittable_list.h:29-35).  Built from
+ * reference constructors; not a scene the reference ships. */
+static scene* build_media_mix() {
+    scene* s = blank_scene(1.0f, background_color::sky, 8);
+    hittable** top = s->d_list;
+    int k = 0;
+    material* white = new lambertian(color(0.73f, 0.73f, 0.73f));
+    material* red = new lambertian(color(0.65f, 0.05f, 0.05f));
+    /* far medium first, then the nearer one that overlaps it */
+    hittable* far_box = new translate(new rotate_y(new box(point3(0, 0, 0), point3(200, 200, 200), white), 20), vec3(150, 50, 300));
+    top[k++] = new constant_medium(far_box, 0.01f, color(0.1f, 0.1f, 0.1f));
+    hittable* near_box = new translate(new box(point3(0, 0, 0), point3(200, 200, 200), white), vec3(200, 80, 150));
+    top[k++] = new constant_medium(near_box, 0.006f, color(0.9f, 0.9f, 0.9f));
+    /* a surface listed AFTER both media, standing inside the nearer one (in front of its far side) */
+    top[k++] = new sphere(point3(300, 180, 250), 60, red);
+    top[k++] = new xz_rect(-200, 800, -200, 900, 0, white);
+    /* and a third medium listed last, in front of everything */
+    hittable* front_box = new box(point3(180, 60, 20), point3(420, 300, 100), white);
+    top[k++] = new constant_medium(front_box, 0.004f, color(0.2f, 0.4f, 0.9f));
+    *s->d_world = new hittable_list(top, k);
+    *s->d_camera = new camera(vec3(278, 278, -600), vec3(290, 160, 250), vec3(0, 1, 0), 40, 1.0f, 0.0f, 10.0f, 0, 1);
+    s->no_hittables = k;
+    return s;
+}
+
 /* door_scene / cup_scene shape (scenes.h:478-523, :576-621): one triangle_mesh + ground sphere, with the
  * flat arrays fed straight into the reference's create_meshes_d (triangle_mesh.h:147) instead of assimp. */
 static scene* build_mesh(const float* verts, int nverts, const unsigned* idx, int ntris, const float* uvs,
@@ -368,6 +395,7 @@ REF_API int ref_scene_named(const char* name) {
     else if (n == "cornell_smoke") s = new cornell_smoke_box_scene;
     else if (n == "triangle") s = new triangle_scene;
     else if (n == "triangles") s = new triangles_scene;
+    else if (n == "media_mix") s = build_media_mix();
     else return -1;
     return register_scene(s);
 }

@@ -21,7 +21,7 @@ import raytracing_gpu_b200 as rt  # noqa: E402
 N_RAYS = 2048
 # scene -> (image width, spp) for the converged reference image (height follows the reference's own rule)
 IMAGES = {"first": (64, 1024), "big1": (80, 1024), "two_perlin": (64, 512), "cornell": (48, 2048), "cornell_smoke": (48, 2048),
-          "earth": (64, 512), "final": (64, 1024), "mesh": (64, 512), "triangles": (64, 256)}
+          "earth": (64, 512), "final": (64, 1024), "mesh": (64, 512), "triangles": (64, 256), "media_mix": (64, 1024)}
 
 
 def build(L, name):
@@ -62,7 +62,10 @@ def main():
     L = helpers.ref_lib()
     assert L is not None, "build oracle/_ref first"
     threads = os.cpu_count() or 1
-    for k, name in enumerate(helpers.NAMED_SCENES + ["earth", "final", "mesh"]):
+    only = [a for a in sys.argv[1:] if not a.startswith("--")]
+    for k, name in enumerate(helpers.NAMED_SCENES + ["earth", "final", "mesh", "media_mix"]):
+        if only and name not in only:
+            continue
         t0 = time.time()
         h = build(L, name)
         assert h >= 0, name
@@ -89,6 +92,8 @@ def main():
 if __name__ == "__main__":
     if "--wide" in sys.argv:
         main_wide()        # only the 256-pixel images (the first set is not regenerated)
+    elif len(sys.argv) > 1:
+        main()             # only the scenes named on the command line
     else:
         main()
         main_wide()

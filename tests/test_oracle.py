@@ -6,7 +6,7 @@ import pytest
 import raytracing_gpu_b200 as rt
 from tests import helpers
 
-ALL = helpers.NAMED_SCENES + ["earth", "final", "mesh"]
+ALL = helpers.NAMED_SCENES + ["earth", "final", "mesh", "media_mix"]   # media_mix: overlapping media, medium listed before a nearer surface
 
 
 def scene_from_golden(name):
