@@ -922,6 +922,7 @@ __global__ void __launch_bounds__(128) k_wide_level(const BNode* __restrict__ no
         }
         uint32_t base = 0, slot = 0;
         if (cnt_internal) { base = atomicAdd(&ctl->n_wide, (uint32_t)cnt_internal); slot = atomicAdd(&ctl->nq[level + 1], (uint32_t)cnt_internal); }
+        RT_DEV_ASSERT(level + 1 < RT_STACK_DEPTH + 2);
         WNode w;
         w.ox = org[0]; w.oy = org[1]; w.oz = org[2];
         w.exps = eb[0] | eb[1] << 8 | eb[2] << 16;
@@ -1357,7 +1358,7 @@ int build_bvh_finish(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t 
 constexpr uint32_t WIDE_MIN_PRIMS = 65536;   // RT_WIDE_AUTO: scenes from this size on walk the 4-wide compressed tree
 
 int build_wide(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t stream) {
-    ds.view.wide = nullptr;
+    ds.view.wide = nullptr; ds.view.n_wide = 0;
     ds.build.n_wide_nodes = 0;
     const uint32_t n = ds.view.n_prims;
     if (bs.wide_nodes > RT_WIDE_ON) { set_error("commit: unknown rt_build_settings::wide_nodes"); return RT_ERR_INVALID; }
@@ -1388,7 +1389,7 @@ int build_wide(DeviceScene& ds, const rt_build_settings& bs, cudaStream_t stream
     RT_CUDA(cudaStreamSynchronize(stream));
     if (h_ctl->nq[levels] != 0) { set_error("bvh build: wide collapse did not finish (internal error)"); return RT_ERR_STATE; }
     ds.view.wide = (const WNode*)ds.wide.p;
-    ds.build.n_wide_nodes = h_ctl->n_wide;
+    ds.build.n_wide_nodes = h_ctl->n_wide; ds.view.n_wide = h_ctl->n_wide;
     ds.build.wide_depth = h_ctl->depth;
     cudaEventElapsedTime(&ds.build.ms_wide, ds.ev[6], ds.ev[7]);
     return RT_OK;

@@ -13,6 +13,16 @@
 
 #include "../../include/rt_b200.h"
 
+// Checked build (tools/build_variant.sh checked -DRT_CHECKED=1): device-side assertions on every index the kernels compute
+// themselves — pool slots, stack depths, continuation records, queue slots.  compute-sanitizer is closed on this pool
+// (profiles/r02_sanitizer.md), so this is the bounds check the round can run.
+#if RT_CHECKED
+#include <cstdio>
+#define RT_DEV_ASSERT(cond) do { if (!(cond)) { printf("RT_DEV_ASSERT failed: %s (%s:%d) block %d thread %d\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, (int)threadIdx.x); __trap(); } } while (0)
+#else
+#define RT_DEV_ASSERT(cond) do { } while (0)
+#endif
+
 namespace rtb {
 
 // 48-byte device primitive (3 x 128-bit).  Parameter order = rt_flat_prim::f (include/rt_flat.h).
@@ -89,6 +99,7 @@ struct SceneView {
     const BNode* nodes;            // nodes[0] = root (n_prims >= 1)
     const WNode* wide;             // non-null: the traversal walks the 4-wide compressed tree instead (wide[0] = root)
     uint32_t n_prims, n_media, n_nodes, n_active_media;
+    uint32_t n_wide;               // wide nodes in use (0 without the wide tree)
     rt_flat_camera camera;
     float background[3];
     uint32_t semantics;            // rt_semantics bits (rt_b200.h); 0 = the reference's behaviour

@@ -157,6 +157,8 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     int sp = 0;
     // shared-memory column of this thread: node words, then RT_SHORT_STACK rows further the entry distances (TC)
     auto push = [&](int n, float tn) {
+        RT_DEV_ASSERT(sp < (SM ? RT_SHORT_STACK : RT_STACK));
+        RT_DEV_ASSERT(n < 0 ? (uint32_t)~n < sv.n_prims : (uint32_t)n < ((V & TV_WIDE) ? sv.n_wide : sv.n_nodes));
         if constexpr (SM) { stack_column[sp * STRIDE] = n; if constexpr (TC) stack_column[(RT_SHORT_STACK + sp) * STRIDE] = __float_as_int(tn); }
         else { node_loc[sp] = n; if constexpr (TC) tn_loc[sp] = tn; }
         sp++;
@@ -209,6 +211,7 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
             if (parked != RT_NODE_DONE) {
                 const int prim = ~parked;
                 parked = RT_NODE_DONE;
+                RT_DEV_ASSERT((uint32_t)prim < sv.n_prims);
                 const DPrim p = sv.prims[prim];
                 const uint32_t chain = prim_chain(p);
                 if (chain != cached_chain) { cached = to_object_space(sv, chain, ray); cached_chain = chain; }
@@ -247,6 +250,7 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
             if constexpr (WIDE) {
                 const WideHits h = wide_step(sv.wide + node, s, t_min, best.t);
                 if (COUNT) cnt->nodes++;
+                RT_DEV_ASSERT(sp + 3 <= RT_STACK);
                 if (h.c[3] != RT_NODE_DONE) stack[sp++] = h.c[3];
                 if (h.c[2] != RT_NODE_DONE) stack[sp++] = h.c[2];
                 if (h.c[1] != RT_NODE_DONE) stack[sp++] = h.c[1];
@@ -256,6 +260,7 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
                 if (COUNT) cnt->nodes++;
                 if (h.h0 && h.h1) {
                     const bool swap = h.t1n < h.t0n;
+                    RT_DEV_ASSERT(sp < RT_STACK);
                     stack[sp++] = swap ? h.c0 : h.c1;
                     node = swap ? h.c1 : h.c0;
                 } else if (h.h0) node = h.c0;
@@ -271,6 +276,7 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
             if (parked != RT_NODE_DONE) {
                 const int prim = ~parked;
                 parked = RT_NODE_DONE;
+                RT_DEV_ASSERT((uint32_t)prim < sv.n_prims);
                 const DPrim p = sv.prims[prim];
                 const uint32_t chain = prim_chain(p);
                 if (chain != cached_chain) { cached = to_object_space(sv, chain, ray); cached_chain = chain; }

@@ -313,6 +313,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
             if (lane == (uint32_t)(__ffs(ms) - 1)) slot = atomicAdd(&pv.c->cont[wr].n, (uint32_t)__popc(ms));
             slot = __shfl_sync(0xffffffffu, slot, __ffs(ms) - 1) + __popc(ms & lt);
             if (suspended) {
+                RT_DEV_ASSERT(slot < pv.capacity && w.sp <= RT_SUSPEND_STACK);
                 if (!resumed) { th = pv.thr[cur][pos]; pv.hit_class[pos] = (uint8_t)Q_HOLE; }
                 pv.cont_o[wr][slot] = o; pv.cont_d[wr][slot] = d; pv.cont_thr[wr][slot] = th;
                 pv.cont_walk[wr][slot] = make_uint4(__float_as_uint(c.t), (uint32_t)c.prim, (uint32_t)w.node, (uint32_t)w.parked);
@@ -327,6 +328,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
             if (mf && lane == (uint32_t)(__ffs(mf) - 1)) k = atomicAdd(&pv.c->n_fin[cur].n, (uint32_t)__popc(mf));
             if (mf) k = __shfl_sync(0xffffffffu, k, __ffs(mf) - 1) + __popc(mf & lt);
             if (finished) {
+                RT_DEV_ASSERT(k < pv.capacity);
                 pos = pv.capacity + k;
                 pv.ray_o[cur][pos] = o; pv.ray_d[cur][pos] = d; pv.thr[cur][pos] = th;
             }
@@ -505,6 +507,7 @@ __device__ __forceinline__ void shade_warp_tiles(const SceneView& sv, const Pool
             const bool goes_on = shade_path(sv, pv, fp, cur, pos, k, (c & (uint32_t)Q_LAST) != 0, out);
             if (class_continues(c)) {
                 const uint32_t dst = base_b + xr;                            // survivors keep tile order
+                RT_DEV_ASSERT(dst < pv.capacity);
                 if (goes_on) { pv.ray_o[next][dst] = out.o; pv.ray_d[next][dst] = out.d; pv.thr[next][dst] = out.thr; }
                 else {   // absorbed after its slot was reserved: a dead slot, counted out of the ray total; its sample slot regenerates one iteration late
                     pv.ray_d[next][dst] = make_float4(0.f, 0.f, 1.f, __uint_as_float(DEAD_BOUNCE << 24));
@@ -610,10 +613,12 @@ __device__ __forceinline__ void shade_block_tiles(const SceneView& sv, const Poo
         const int cls_next = class_of(tile_next);    // in flight while this tile's results are stored
         if (continues) {
             const uint32_t dst = s_base_b + s_wcont[warp] + __popc(mc & lt);
+            RT_DEV_ASSERT(dst < pv.capacity);
             pv.ray_o[next][dst] = out.o; pv.ray_d[next][dst] = out.d; pv.thr[next][dst] = out.thr;
         }
         if (terminated) {
             const uint32_t r = s_wterm[warp] + __popc(mt & lt);
+            RT_DEV_ASSERT(r >= s_nregen || s_base_f + s_nregen <= pv.capacity);
             if (r < s_nregen) start_path(sv, pv, fp, next, pv.capacity - (s_base_f + s_nregen) + r, s_g0 + r);
         }
         tile = tile_next;
