@@ -162,6 +162,10 @@ typedef struct rt_build_settings {
 int rt_scene_commit(rt_scene* s, int device, rt_build_stats* stats_or_null);
 int rt_scene_commit_ex(rt_scene* s, int device, const rt_build_settings* settings_or_null, rt_build_stats* stats_or_null);
 
+/* Test hook: the (nth + 1)-th device allocation the library makes from now on fails with an out-of-memory error (nth < 0:
+ * off).  Error paths must then return RT_ERR_CUDA, leak nothing and leave the scene usable for a retry. */
+void rt_debug_fail_allocation(int nth);
+
 /* Copies the binary BVH of the committed scene to the host: rt_build_stats::n_nodes records of 64 bytes (16 words:
  * child 0 lo.x hi.x lo.y hi.y | child 1 lo.x hi.x lo.y hi.y | child 0 lo.z hi.z, child 1 lo.z hi.z | child codes, 2 pad words;
  * a child code >= 0 is a node index, < 0 the complement of a primitive's position in leaf order).  For tools and tests

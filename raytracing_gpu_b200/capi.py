@@ -130,7 +130,7 @@ def lib():
         "rt_scene_export_size": (C.c_size_t, [vp]), "rt_scene_export": (i32, [vp, vp, C.c_size_t]),
         "rt_image_height": (i32, [i32, f32]), "rt_scene_commit": (i32, [vp, i32, C.POINTER(BuildStats)]),
         "rt_scene_commit_ex": (i32, [vp, i32, C.POINTER(BuildSettings), C.POINTER(BuildStats)]),
-        "rt_measure_fp32_peak": (i32, [i32, C.POINTER(C.c_double)]), "rt_scene_bvh_nodes": (i32, [vp, vp, C.c_size_t]),
+        "rt_measure_fp32_peak": (i32, [i32, C.POINTER(C.c_double)]), "rt_debug_fail_allocation": (None, [i32]), "rt_scene_bvh_nodes": (i32, [vp, vp, C.c_size_t]),
         "rt_first_hit": (i32, [vp, vp, i32, f32, vp, vp, vp]), "rt_first_hit_static": (i32, [vp, vp, i32, f32, vp, vp, vp]),
         "rt_render": (i32, [vp, C.POINTER(RenderSettings), vp, C.POINTER(RenderStats)]),
         "rt_render_device": (i32, [vp, C.POINTER(RenderSettings), vp, vp, C.POINTER(RenderStats)]),

@@ -11,6 +11,7 @@
 #include "device_scene.cuh"
 #include "traverse.cuh"
 
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -26,6 +27,16 @@ bool cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
     set_error(buf);
     cudaGetLastError();   // clear the sticky-less error state
     return true;
+}
+
+// fault injection for the error-path tests: the n-th growing DevBuf::reserve from now fails with cudaErrorMemoryAllocation
+static std::atomic<int> g_alloc_fault{-1};
+bool alloc_fault_due() {
+    int v = g_alloc_fault.load();
+    while (v >= 0) {
+        if (g_alloc_fault.compare_exchange_weak(v, v - 1)) return v == 0;
+    }
+    return false;
 }
 
 void device_scene_destroy(DeviceScene* d) {
@@ -340,6 +351,8 @@ extern "C" int rt_scene_commit_ex(rt_scene* s, int device, const rt_build_settin
     if (stats) *stats = slot->build;
     return RT_OK;
 }
+
+extern "C" void rt_debug_fail_allocation(int nth) { g_alloc_fault.store(nth); }
 
 extern "C" int rt_scene_commit(rt_scene* s, int device, rt_build_stats* stats) { return rt_scene_commit_ex(s, device, nullptr, stats); }
 

@@ -109,6 +109,7 @@ struct SceneView {
 
 // Grow-only device / pinned-host buffers: a re-commit of a scene reuses every allocation of the previous one
 // (cudaMalloc / cudaFree synchronise the device; round 1 paid ~40 of them per commit).
+bool alloc_fault_due();   // device_api.cu: rt_debug_fail_allocation's countdown (tests inject an out-of-memory error)
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
@@ -117,7 +118,7 @@ struct DevBuf {
         if (p) cudaFree(p);
         p = nullptr; cap = 0;
         const size_t want = bytes + bytes / 4 + 256;
-        const cudaError_t e = cudaMalloc(&p, want);
+        const cudaError_t e = alloc_fault_due() ? cudaErrorMemoryAllocation : cudaMalloc(&p, want);
         if (e == cudaSuccess) cap = want;
         return e;
     }

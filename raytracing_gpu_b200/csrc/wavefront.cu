@@ -708,6 +708,8 @@ int extend_occupancy(int v, int* occ) {
     return RT_OK;
 }
 
+template <class T> cudaError_t pool_alloc(T** p, size_t bytes) { return alloc_fault_due() ? cudaErrorMemoryAllocation : cudaMalloc((void**)p, bytes); }
+
 int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
     RenderPool* p = new RenderPool;
     p->device = ds.device;
@@ -716,13 +718,13 @@ int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
     p->suspend_below = suspend_below;
     const size_t slots = p->suspend_below ? 2 * (size_t)capacity : capacity;   // + the finished-resumed region at positions >= capacity
     for (int b = 0; b < 2; b++) {
-        RT_CUDA(cudaMalloc(&p->v.ray_o[b], sizeof(float4) * slots));
-        RT_CUDA(cudaMalloc(&p->v.ray_d[b], sizeof(float4) * slots));
-        RT_CUDA(cudaMalloc(&p->v.thr[b], sizeof(float4) * slots));
+        RT_CUDA(pool_alloc(&p->v.ray_o[b], sizeof(float4) * slots));
+        RT_CUDA(pool_alloc(&p->v.ray_d[b], sizeof(float4) * slots));
+        RT_CUDA(pool_alloc(&p->v.thr[b], sizeof(float4) * slots));
     }
-    RT_CUDA(cudaMalloc(&p->v.hit, sizeof(uint2) * slots));
-    RT_CUDA(cudaMalloc(&p->v.hit_class, sizeof(uint8_t) * slots));
-    RT_CUDA(cudaMalloc(&p->v.c, sizeof(Counters)));
+    RT_CUDA(pool_alloc(&p->v.hit, sizeof(uint2) * slots));
+    RT_CUDA(pool_alloc(&p->v.hit_class, sizeof(uint8_t) * slots));
+    RT_CUDA(pool_alloc(&p->v.c, sizeof(Counters)));
     RT_CUDA(cudaHostAlloc(&p->h_live, sizeof(uint32_t) * POLL_SLOTS, cudaHostAllocMapped));
     RT_CUDA(cudaHostAlloc(&p->h_counters, sizeof(Counters), cudaHostAllocDefault));
     for (auto& e : p->poll_ev) RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -732,12 +734,12 @@ int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
     RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
     if (p->suspend_below) {
         for (int b = 0; b < 2; b++) {
-            RT_CUDA(cudaMalloc(&p->v.cont_walk[b], sizeof(uint4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_o[b], sizeof(float4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_d[b], sizeof(float4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_thr[b], sizeof(float4) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_sp[b], sizeof(uint8_t) * capacity));
-            RT_CUDA(cudaMalloc(&p->v.cont_stack[b], sizeof(int) * (size_t)capacity * RT_SUSPEND_STACK));
+            RT_CUDA(pool_alloc(&p->v.cont_walk[b], sizeof(uint4) * capacity));
+            RT_CUDA(pool_alloc(&p->v.cont_o[b], sizeof(float4) * capacity));
+            RT_CUDA(pool_alloc(&p->v.cont_d[b], sizeof(float4) * capacity));
+            RT_CUDA(pool_alloc(&p->v.cont_thr[b], sizeof(float4) * capacity));
+            RT_CUDA(pool_alloc(&p->v.cont_sp[b], sizeof(uint8_t) * capacity));
+            RT_CUDA(pool_alloc(&p->v.cont_stack[b], sizeof(int) * (size_t)capacity * RT_SUSPEND_STACK));
         }
         RT_CUDA((cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend_defer<false, false>, EXTEND_BLOCK, 0)));
         p->grid_extend = sms * std::max(occ, 1);
@@ -784,7 +786,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     if (ds.pool && (ds.pool->v.capacity != capacity || ds.pool->suspend_below != susp)) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
     if (!ds.pool) {
         const int rc = pool_create(ds, capacity, susp);
-        if (rc < 0) return rc;
+        if (rc < 0) { render_pool_destroy(ds.pool); ds.pool = nullptr; return rc; }   // a half-built pool is never kept
     }
     RenderPool& P = *ds.pool;
     const int variant = extend_variant(ds, st);
