@@ -521,9 +521,11 @@ __device__ __forceinline__ void shade_warp_tiles(const SceneView& sv, const Pool
     }
 }
 
+#if RT_EXPERIMENTS
 __global__ void __launch_bounds__(SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<false>(sv, pv, fp, cur); }
 // shade of the deferred extend: holes in the tiles and the finished-resumed region behind the pool
 __global__ void __launch_bounds__(SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<true>(sv, pv, fp, cur); }
+#endif
 
 // The default shade: a BLOCK sorts a 256-path tile by class in shared memory (a warp shades one class), thread 0 allocates
 // between two barriers — five __syncthreads per tile.
@@ -680,9 +682,15 @@ int extend_variant(const DeviceScene& ds, const rt_render_settings& st) {
     return v;
 }
 
+// The measured-and-rejected variants (traversal bits 1-7, the warp-tile shade) are compiled only with -DRT_EXPERIMENTS=1
+// (tools/build_variant.sh exp -DRT_EXPERIMENTS=1): the product library carries the default kernels and the wide-tree ones.
+#ifndef RT_EXPERIMENTS
+#define RT_EXPERIMENTS 0
+#endif
 template <bool COUNT> void launch_extend(int v, int grid, cudaStream_t s, const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
     switch (v) {
     case 0: k_extend<COUNT, 0><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+#if RT_EXPERIMENTS
     case 1: k_extend<COUNT, 1><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 2: k_extend<COUNT, 2><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 3: k_extend<COUNT, 3><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
@@ -690,12 +698,14 @@ template <bool COUNT> void launch_extend(int v, int grid, cudaStream_t s, const 
     case 5: k_extend<COUNT, 5><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 6: k_extend<COUNT, 6><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 7: k_extend<COUNT, 7><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+#endif
     default: k_extend<COUNT, TV_WIDE><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     }
 }
 int extend_occupancy(int v, int* occ) {
     switch (v) {
     case 0: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 0>, EXTEND_BLOCK, 0)); break;
+#if RT_EXPERIMENTS
     case 1: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 1>, EXTEND_BLOCK, 0)); break;
     case 2: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 2>, EXTEND_BLOCK, 0)); break;
     case 3: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 3>, EXTEND_BLOCK, 0)); break;
@@ -703,6 +713,7 @@ int extend_occupancy(int v, int* occ) {
     case 5: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 5>, EXTEND_BLOCK, 0)); break;
     case 6: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 6>, EXTEND_BLOCK, 0)); break;
     case 7: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 7>, EXTEND_BLOCK, 0)); break;
+#endif
     default: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, TV_WIDE>, EXTEND_BLOCK, 0)); break;
     }
     return RT_OK;
@@ -743,13 +754,17 @@ int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
         }
         RT_CUDA((cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_extend_defer<false, false>, EXTEND_BLOCK, 0)));
         p->grid_extend = sms * std::max(occ, 1);
+#if RT_EXPERIMENTS
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_defer, SHADE_BLOCK, 0));
         p->grid_shade = sms * std::max(occ, 1);
+#endif
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_block_defer, SHADE_BLOCK, 0));
         p->grid_shade_block = sms * std::max(occ, 1);
     } else {
+#if RT_EXPERIMENTS
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, SHADE_BLOCK, 0));
         p->grid_shade = sms * std::max(occ, 1);
+#endif
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_block, SHADE_BLOCK, 0));
         p->grid_shade_block = sms * std::max(occ, 1);
     }
@@ -790,6 +805,12 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     }
     RenderPool& P = *ds.pool;
     const int variant = extend_variant(ds, st);
+#if !RT_EXPERIMENTS
+    if ((variant != 0 && variant != TV_WIDE) || (st.debug_flags & RT_DEBUG_WARP_SHADE)) {
+        set_error("render: this variant (rt_render_settings::traversal bits / RT_DEBUG_WARP_SHADE) is compiled only into the experiments build (-DRT_EXPERIMENTS=1)");
+        return RT_ERR_UNSUPPORTED;
+    }
+#endif
     if (!P.suspend_below && P.extend_variant != variant) {
         int occ = 0, sms = 0;
         RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds.device));
@@ -841,8 +862,11 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         if (block_shade) {
             if (P.suspend_below) k_shade_block_defer<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
             else k_shade_block<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
-        } else if (P.suspend_below) k_shade_defer<<<P.grid_shade, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
+        }
+#if RT_EXPERIMENTS
+        else if (P.suspend_below) k_shade_defer<<<P.grid_shade, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
         else k_shade<<<P.grid_shade, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
+#endif
         if (timed && tick() < 0) return RT_ERR_CUDA;
         k_turnover<<<1, 1, 0, s>>>(P.v, cur, fp.total_samples, d_live + slot);
         return RT_OK;

