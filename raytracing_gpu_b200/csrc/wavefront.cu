@@ -123,6 +123,9 @@ struct FrameParams {
     uint32_t tile_index, tile_count;    // tile-split: film blocks b with b % tile_count == tile_index (tile_count <= 1: all)
 };
 
+#ifndef RT_EXPERIMENTS
+#define RT_EXPERIMENTS 0
+#endif
 constexpr int EXTEND_BLOCK = 128;
 constexpr uint32_t SUSPEND_MIN_PRIMS = 65536, SUSPEND_BELOW_DEFAULT = 8;
 #ifndef EXTEND_MIN_BLOCKS
@@ -676,7 +679,8 @@ uint32_t suspend_threshold(const DeviceScene& ds, const rt_render_settings& st) 
 
 // traversal variant of k_extend: the caller's, else the default; the shared-memory stack only for trees it can hold
 int extend_variant(const DeviceScene& ds, const rt_render_settings& st) {
-    if (ds.view.wide) return TV_WIDE;   // the committed scene carries the 4-wide compressed tree: one variant walks it
+    if (ds.view.wide)   // the committed scene carries the 4-wide compressed tree (A/B: entry-distance culling of its stack entries)
+        return TV_WIDE | (((st.traversal & RT_TRAVERSAL_FORCE) && RT_EXPERIMENTS) ? (int)(st.traversal & TV_TCULL) : 0);
     int v = (st.traversal & RT_TRAVERSAL_FORCE) ? (int)(st.traversal & 7u) : (int)RT_TRAVERSAL_DEFAULT_BITS;
     if (ds.build.bvh_depth == 0 || ds.build.bvh_depth + 1 > RT_SHORT_STACK) v &= ~TV_SMEM;
     return v;
@@ -684,9 +688,6 @@ int extend_variant(const DeviceScene& ds, const rt_render_settings& st) {
 
 // The measured-and-rejected variants (traversal bits 1-7, the warp-tile shade) are compiled only with -DRT_EXPERIMENTS=1
 // (tools/build_variant.sh exp -DRT_EXPERIMENTS=1): the product library carries the default kernels and the wide-tree ones.
-#ifndef RT_EXPERIMENTS
-#define RT_EXPERIMENTS 0
-#endif
 template <bool COUNT> void launch_extend(int v, int grid, cudaStream_t s, const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
     switch (v) {
     case 0: k_extend<COUNT, 0><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
@@ -698,6 +699,7 @@ template <bool COUNT> void launch_extend(int v, int grid, cudaStream_t s, const 
     case 5: k_extend<COUNT, 5><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 6: k_extend<COUNT, 6><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 7: k_extend<COUNT, 7><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 9: k_extend<COUNT, 9><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
 #endif
     default: k_extend<COUNT, TV_WIDE><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     }
@@ -713,6 +715,7 @@ int extend_occupancy(int v, int* occ) {
     case 5: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 5>, EXTEND_BLOCK, 0)); break;
     case 6: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 6>, EXTEND_BLOCK, 0)); break;
     case 7: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 7>, EXTEND_BLOCK, 0)); break;
+    case 9: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 9>, EXTEND_BLOCK, 0)); break;
 #endif
     default: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, TV_WIDE>, EXTEND_BLOCK, 0)); break;
     }
@@ -806,7 +809,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     RenderPool& P = *ds.pool;
     const int variant = extend_variant(ds, st);
 #if !RT_EXPERIMENTS
-    if ((variant != 0 && variant != TV_WIDE) || (st.debug_flags & RT_DEBUG_WARP_SHADE)) {
+    if ((variant != 0 && variant != TV_WIDE) || (st.debug_flags & RT_DEBUG_WARP_SHADE)) {   // (unreachable for variant here; the flag is)
         set_error("render: this variant (rt_render_settings::traversal bits / RT_DEBUG_WARP_SHADE) is compiled only into the experiments build (-DRT_EXPERIMENTS=1)");
         return RT_ERR_UNSUPPORTED;
     }

@@ -71,4 +71,7 @@ if not deferred:
         run(f"defer_{below}", extend_defer=below + 1)
 else:
     run("defer_off", extend_defer=rt.capi.DEFER_OFF)
+    run("defer_off+tcull", extend_defer=rt.capi.DEFER_OFF, traversal=F | 1)
+    for below in (4, 12, 16, 20):
+        run(f"defer_{below}", extend_defer=below + 1)
     run("defer_off+warp_shade", extend_defer=rt.capi.DEFER_OFF, debug_flags=rt.capi.DEBUG_WARP_SHADE)
