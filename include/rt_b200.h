@@ -230,7 +230,8 @@ enum rt_traversal_bits { RT_TRAVERSAL_FORCE = 0x100, RT_TRAVERSAL_DEFAULT_BITS =
 enum rt_debug_flags {
     RT_DEBUG_NO_GRAPH = 1,     /* direct kernel launches instead of the CUDA graph of 8 iterations */
     RT_DEBUG_RASTER_FILM = 2,  /* samples walk the film row by row instead of in 8x4 tiles */
-    RT_DEBUG_WARP_SHADE = 4    /* the barrier-free warp-tile shade kernel (measured slower than the block-tile default: A/B only) */
+    RT_DEBUG_WARP_SHADE = 4,   /* the barrier-free warp-tile shade kernel (measured slower than the block-tile default: A/B only) */
+    RT_DEBUG_BIN_SHADE = 8     /* class-binned shade: k_bin lists the paths of each material class, warps shade class-pure runs of 32 */
 };
 
 typedef struct rt_render_stats {

@@ -57,6 +57,7 @@ struct __align__(128) Counters {
     struct { uint32_t n, pad[31]; } cont[2];      // continuation records in list b (written by the extend of iterations with cur = b)
     struct { uint32_t n, pad[31]; } n_fin[2];     // resumed paths that finished their walk in this iteration: region [capacity, capacity + n) of pool b
     struct { uint32_t n, pad[31]; } n_dead[2];    // dead slots shade wrote into pool b (not path segments: subtracted from total_rays)
+    struct { uint32_t n, pad[31]; } bin_n[8];     // class-binned shade: entries in each bin's list this iteration (k_bin)
 };
 
 struct PoolView {
@@ -73,6 +74,8 @@ struct PoolView {
     float4* cont_thr[2];   //   throughput + pixel
     uint8_t* cont_sp[2];   // stack entries
     int* cont_stack[2];    // [entry * capacity + record]
+    uint32_t* bin_list;    // class-binned shade: NBINS lists of pool positions, bin b at [b * bin_stride, ...)
+    uint32_t bin_stride;
     Counters* c;
     uint32_t capacity;
 };
@@ -84,7 +87,7 @@ struct RenderPool {
     Counters* h_counters = nullptr;   // pinned copy for stats
     cudaEvent_t poll_ev[POLL_SLOTS]{};
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    int grid_extend = 0, grid_shade = 0, grid_shade_block = 0;
+    int grid_extend = 0, grid_shade = 0, grid_shade_block = 0, grid_shade_bins = 0, grid_bin = 0;
     int extend_variant = -1;               // traversal variant the extend grid was sized for
     cudaGraphExec_t graph_exec = nullptr;   // GRAPH_ITERS wavefront iterations as one CUDA graph (render_impl)
     cudaStream_t capture_stream = nullptr;
@@ -97,7 +100,7 @@ void render_pool_destroy(RenderPool* p) {
     if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
     if (p->capture_stream) cudaStreamDestroy(p->capture_stream);
     for (int b = 0; b < 2; b++) { cudaFree(p->v.ray_o[b]); cudaFree(p->v.ray_d[b]); cudaFree(p->v.thr[b]); }
-    cudaFree(p->v.hit); cudaFree(p->v.hit_class); cudaFree(p->v.c);
+    cudaFree(p->v.hit); cudaFree(p->v.hit_class); cudaFree(p->v.bin_list); cudaFree(p->v.c);
     for (int b = 0; b < 2; b++) {
         cudaFree(p->v.cont_walk[b]); cudaFree(p->v.cont_o[b]); cudaFree(p->v.cont_d[b]); cudaFree(p->v.cont_thr[b]);
         cudaFree(p->v.cont_sp[b]); cudaFree(p->v.cont_stack[b]);
@@ -213,6 +216,23 @@ __device__ __forceinline__ uint8_t hit_class_of(const SceneView& sv, const Close
     return (uint8_t)q;
 }
 
+constexpr int NBINS = 7, BIN_NONE = 7, BIN_CONT = 4;       // bins 0..3 continue (lambertian, metal, dielectric, isotropic), 4..6 end (light, miss, nothing to do)
+constexpr int BIN_THREADS = 1024, BIN_WARPS = BIN_THREADS / 32, BIN_ROUNDS = 8, BIN_SPAN = BIN_THREADS * BIN_ROUNDS;
+static_assert(BIN_WARPS >= 7 && BIN_ROUNDS <= 8, "one warp per bin scans; 4 bits per round in a 32-bit word");
+constexpr int BIN_CLAIM = 4;                               // rounds of 32 list entries a shading warp claims at once
+
+constexpr uint32_t bin_of_class(uint32_t c) {
+    const uint32_t k = c & 7u;
+    if (k == (uint32_t)Q_HOLE) return (uint32_t)BIN_NONE;
+    if (k == (uint32_t)Q_MISS) return 5u;
+    if (k == (uint32_t)Q_LIGHT) return 4u;
+    if (k == (uint32_t)Q_DEAD || (c & (uint32_t)Q_LAST)) return 6u;       // absorbed earlier / depth exhausted: black, only regenerates
+    return k == 1u + RT_MAT_ISOTROPIC ? 3u : k - 1u;                       // 1 + {lambertian 0, metal 1, dielectric 2}
+}
+constexpr uint32_t bin_table(uint32_t first) { uint32_t t = 0; for (uint32_t c = 0; c < 8; c++) t |= bin_of_class(first + c) << (4 * c); return t; }
+constexpr uint32_t BIN_TABLE_LO = bin_table(0), BIN_TABLE_HI = bin_table(8);   // class byte -> bin, 4 bits each
+__device__ __forceinline__ uint32_t bin_of(uint32_t c) { return (((c & 8u) ? BIN_TABLE_HI : BIN_TABLE_LO) >> (4u * (c & 7u))) & 7u; }
+
 // ---- extend ---------------------------------------------------------------------------------------
 // V: traversal variant (traverse.cuh: TV_TCULL | TV_SMEM | TV_MINMAX)
 template <bool COUNT, int V>
@@ -245,9 +265,11 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
             return draw4(key, RT_STREAM_MEDIUM, m).x;
         }, &tc, in_range && !dead, column);
         if (COUNT) slots += 32ull * __reduce_max_sync(0xffffffffu, tc.nodes - nodes_before);   // node steps the warp paid for
+        uint32_t cls = (uint32_t)Q_HOLE;
         if (in_range) {
             pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
-            pv.hit_class[pos] = dead ? (uint8_t)Q_DEAD : hit_class_of(sv, c, sb >> 24, fp.max_depth);
+            cls = dead ? (uint32_t)Q_DEAD : (uint32_t)hit_class_of(sv, c, sb >> 24, fp.max_depth);
+            pv.hit_class[pos] = (uint8_t)cls;
         }
     }
     if (COUNT) {
@@ -336,6 +358,7 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
                 pv.ray_o[cur][pos] = o; pv.ray_d[cur][pos] = d; pv.thr[cur][pos] = th;
             }
         }
+        uint32_t cls = (uint32_t)Q_HOLE;
         if (finished) {
             const uint32_t sb = __float_as_uint(d.w);
             // the free-flight draw of medium m is keyed (pixel, sample, bounce, m); the pixel is only fetched when a ray really crosses a boundary
@@ -344,7 +367,8 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
                 return draw4(key, RT_STREAM_MEDIUM, m).x;
             });
             pv.hit[pos] = make_uint2(__float_as_uint(c.t), (uint32_t)c.prim);
-            pv.hit_class[pos] = dead ? (uint8_t)Q_DEAD : hit_class_of(sv, c, sb >> 24, fp.max_depth);
+            cls = dead ? (uint32_t)Q_DEAD : (uint32_t)hit_class_of(sv, c, sb >> 24, fp.max_depth);
+            pv.hit_class[pos] = (uint8_t)cls;
         }
     }
     if (COUNT) {
@@ -633,18 +657,158 @@ __device__ __forceinline__ void shade_block_tiles(const SceneView& sv, const Poo
 __global__ void __launch_bounds__(SHADE_BLOCK) k_shade_block(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_block_tiles<false>(sv, pv, fp, cur); }
 __global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_block_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_block_tiles<true>(sv, pv, fp, cur); }
 
+// ---- class-binned shade (RT_DEBUG_BIN_SHADE) ----------------------------------------------------------
+// VERDICT r1 #3, option A: no sort and no allocation inside shade.  k_bin lists the pool positions of every class ("bin")
+// once per iteration; k_shade_bins walks the concatenation of the lists 32 entries at a time, so a warp shades paths of ONE
+// class, and because the class byte says whether a path goes on, where its result lands is a pure function of its list
+// index: the j-th entry of continuing bin b goes to slot (entries of the continuing bins before b) + j of the next pool,
+// the r-th ending path regenerates sample next_sample + r.  No __syncthreads in the loop, no atomics but the work claim
+// (and one per warp that meets an absorbed path: its reserved slot becomes a dead slot, as in the warp-tile kernel).
+// lanes whose 3-bit value is `k`, from the three bit ballots
+__device__ __forceinline__ uint32_t mask_of(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t k) {
+    return ((k & 1u) ? b0 : ~b0) & ((k & 2u) ? b1 : ~b1) & ((k & 4u) ? b2 : ~b2);
+}
+
+template <bool DEFER>
+__global__ void __launch_bounds__(BIN_THREADS) k_bin(PoolView pv, int cur) {
+    __shared__ uint32_t s_cnt[8][BIN_WARPS];         // [bin][warp]: counts, then list offsets
+    const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
+    const uint32_t n = n_pool + (DEFER ? pv.c->n_fin[cur].n : 0u);
+    const uint32_t span = blockIdx.x * (uint32_t)BIN_SPAN;
+    if (span >= n) return;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
+    const uint32_t base = span + warp * 32u * BIN_ROUNDS;      // a warp lists 32 * BIN_ROUNDS consecutive paths
+    auto pos_at = [&](uint32_t idx) { return DEFER && idx >= n_pool ? pv.capacity + (idx - n_pool) : pos_of(idx, n_b, n_pool, pv.capacity); };
+    // lane k counts bin k & 7: the lanes of bin k are (b0 ^ x0) & (b1 ^ x1) & (b2 ^ x2) of the three bit ballots
+    const uint32_t x0 = (lane & 1u) ? 0u : ~0u, x1 = (lane & 2u) ? 0u : ~0u, x2 = (lane & 4u) ? 0u : ~0u;
+    uint32_t bins = 0, cnt = 0;                      // this lane's bin per round, 4 bits each
+    uint32_t per_round[BIN_ROUNDS / 4] = {};         // lane k: entries of bin k in each round, 8 bits each
+    #pragma unroll
+    for (int r = 0; r < BIN_ROUNDS; r++) {
+        const uint32_t idx = base + 32u * r + lane;
+        const uint32_t b = idx < n ? bin_of(pv.hit_class[pos_at(idx)]) : (uint32_t)BIN_NONE;
+        bins |= b << (4 * r);
+        const uint32_t b0 = __ballot_sync(0xffffffffu, b & 1u), b1 = __ballot_sync(0xffffffffu, b & 2u), b2 = __ballot_sync(0xffffffffu, b & 4u);
+        const uint32_t k = __popc((b0 ^ x0) & (b1 ^ x1) & (b2 ^ x2));
+        cnt += k;
+        per_round[r / 4] |= k << (8 * (r & 3));
+    }
+    if (lane < 8) s_cnt[lane][warp] = cnt;
+    __syncthreads();
+    if (warp < NBINS) {                              // warp b: exclusive scan of bin b over the block's warps, one atomic for the block
+        const uint32_t v = lane < (uint32_t)BIN_WARPS ? s_cnt[warp][lane] : 0u;
+        uint32_t x = v;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)lane >= o) x += y; }
+        uint32_t at = 0;
+        if (lane == 31 && x) at = atomicAdd(&pv.c->bin_n[warp].n, x);
+        at = __shfl_sync(0xffffffffu, at, 31);
+        if (lane < (uint32_t)BIN_WARPS) s_cnt[warp][lane] = at + x - v;
+    }
+    __syncthreads();
+    uint32_t cursor = s_cnt[lane & 7u][warp];        // lane k: where this warp's next entry of bin k goes (row 7 is never used)
+    #pragma unroll
+    for (int r = 0; r < BIN_ROUNDS; r++) {
+        const uint32_t b = (bins >> (4 * r)) & 7u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, b);
+        const uint32_t at = __shfl_sync(0xffffffffu, cursor, b) + __popc(peers & lt);
+        cursor += (per_round[r / 4] >> (8 * (r & 3))) & 0xffu;
+        if (b != (uint32_t)BIN_NONE) {
+            RT_DEV_ASSERT(at < pv.bin_stride);
+            pv.bin_list[(size_t)b * pv.bin_stride + at] = pos_at(base + 32u * r + lane);
+        }
+    }
+}
+
+template <bool DEFER>
+__global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_bins(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+    __shared__ uint32_t s_work[NBINS + 1];           // work index where bin b starts (each bin padded to whole warps)
+    __shared__ uint32_t s_n[NBINS], s_rank[NBINS];   // entries of bin b; entries of the bins of its group (continuing / ending) before it
+    const int next = cur ^ 1;
+    if (threadIdx.x == 0) {
+        uint32_t w = 0, rc = 0, rt = 0;
+        for (int b = 0; b < NBINS; b++) {
+            const uint32_t nb = pv.c->bin_n[b].n;
+            s_work[b] = w; s_n[b] = nb;
+            w += (nb + 31u) & ~31u;
+            if (b < BIN_CONT) { s_rank[b] = rc; rc += nb; } else { s_rank[b] = rt; rt += nb; }
+        }
+        s_work[NBINS] = w;
+    }
+    __syncthreads();                                  // the only barrier: once per block
+    const uint32_t n_work = s_work[NBINS];
+    const uint32_t n_end = s_rank[NBINS - 1] + s_n[NBINS - 1];
+    const unsigned long long g_first = pv.c->next_sample;     // no shade warp moves the cursor: k_turnover adds n_end
+    const uint32_t n_regen = g_first < fp.total_samples ? (uint32_t)min((unsigned long long)n_end, fp.total_samples - g_first) : 0u;
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t w0 = warp_claim(&pv.c->cur_shade, 32u * BIN_CLAIM);
+    while (w0 < n_work) {
+        uint32_t w_next = 0;
+        if (lane == 0) w_next = atomicAdd(&pv.c->cur_shade, 32u * BIN_CLAIM);   // in flight while this claim is shaded
+        #pragma unroll 1
+        for (int r = 0; r < BIN_CLAIM; r++) {
+            const uint32_t w = w0 + 32u * r;
+            if (w >= n_work) break;
+            uint32_t b = 0;
+            #pragma unroll
+            for (int k = 1; k < NBINS; k++) b += w >= s_work[k];
+            const uint32_t j = w - s_work[b] + lane;
+            const bool valid = j < s_n[b];                        // false: padding of the bin's last warp
+            const uint32_t part = __ballot_sync(0xffffffffu, valid);
+            if (!valid) continue;
+            const uint32_t pos = pv.bin_list[(size_t)b * pv.bin_stride + j];
+            const uint32_t rank = s_rank[b] + j;
+            if (b < (uint32_t)BIN_CONT) {
+                ShadeOut out;
+                const bool goes_on = shade_path(sv, pv, fp, cur, pos, 1u, false, out);   // the class only matters for paths that end
+                RT_DEV_ASSERT(rank < pv.capacity);
+                if (goes_on) { pv.ray_o[next][rank] = out.o; pv.ray_d[next][rank] = out.d; pv.thr[next][rank] = out.thr; }
+                else {   // absorbed (metal scattering into the surface): a dead slot, regenerated one iteration late
+                    pv.ray_d[next][rank] = make_float4(0.f, 0.f, 1.f, __uint_as_float(DEAD_BOUNCE << 24));
+                    pv.ray_o[next][rank] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                const uint32_t md = __ballot_sync(part, !goes_on);
+                if (md && lane == (uint32_t)(__ffs(md) - 1)) atomicAdd(&pv.c->n_dead[next].n, (uint32_t)__popc(md));
+            } else {
+                ShadeOut out;
+                if (b != 6u) shade_path(sv, pv, fp, cur, pos, b == 5u ? (uint32_t)Q_MISS : (uint32_t)Q_LIGHT, false, out);
+                if (rank < n_regen) start_path(sv, pv, fp, next, pv.capacity - n_regen + rank, g_first + rank);
+            }
+        }
+        w0 = __shfl_sync(0xffffffffu, w_next, 0);
+    }
+}
+
 // ---- turnover -------------------------------------------------------------------------------------
-__global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out) {
+__global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out, int binned) {
     Counters* c = pv.c;
-    c->total_rays += c->n_bounce[cur] + c->n_fresh[cur] - c->n_dead[cur].n;
+    // every load first (they are independent; a store in between would serialise them), then the stores
+    uint32_t bins[NBINS];
+    #pragma unroll
+    for (int b = 0; b < NBINS; b++) bins[b] = binned ? c->bin_n[b].n : 0u;
+    const uint32_t n_b = c->n_bounce[cur], n_f = c->n_fresh[cur], n_d = c->n_dead[cur].n, n_cont = c->cont[cur].n;
+    uint32_t n_next = c->n_bounce[cur ^ 1];
+    unsigned long long cursor = c->next_sample;
+    const unsigned long long rays = c->total_rays, iter_begin = c->iter_begin;
+    if (binned) {   // k_shade_bins allocates by list index: the totals are the bin sizes
+        uint32_t goes_on = 0, ends = 0;
+        #pragma unroll
+        for (int b = 0; b < NBINS; b++) { (b < BIN_CONT ? goes_on : ends) += bins[b]; c->bin_n[b].n = 0; }
+        n_next = goes_on;
+        cursor += ends;
+        c->n_bounce[cur ^ 1] = n_next;
+        c->next_sample = cursor;
+    }
+    c->total_rays = rays + n_b + n_f - n_d;
     c->n_bounce[cur] = 0; c->n_fresh[cur] = 0; c->n_dead[cur].n = 0;
-    const unsigned long long started = min(c->next_sample, total_samples);   // samples regenerated by this iteration's shade
-    c->n_fresh[cur ^ 1] = (uint32_t)(started - c->iter_begin);
+    const unsigned long long started = min(cursor, total_samples);   // samples regenerated by this iteration's shade
+    const uint32_t fresh_next = (uint32_t)(started - iter_begin);
+    c->n_fresh[cur ^ 1] = fresh_next;
     c->iter_begin = started;
     c->cur_extend = 0; c->cur_shade = 0;
     c->cont[cur ^ 1].n = 0;       // consumed by this iteration's extend; the next iteration's extend appends to it
     c->n_fin[cur].n = 0;
-    *live_out = c->n_bounce[cur ^ 1] + c->n_fresh[cur ^ 1] + c->cont[cur].n;   // + the suspended paths the next extend resumes
+    *live_out = n_next + fresh_next + n_cont;   // + the suspended paths the next extend resumes
 }
 
 __global__ void k_scale(const float* sums, float* out, size_t n, float scale) {
@@ -738,6 +902,9 @@ int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
     }
     RT_CUDA(pool_alloc(&p->v.hit, sizeof(uint2) * slots));
     RT_CUDA(pool_alloc(&p->v.hit_class, sizeof(uint8_t) * slots));
+    RT_CUDA(pool_alloc(&p->v.bin_list, sizeof(uint32_t) * slots * NBINS));
+    p->v.bin_stride = (uint32_t)slots;
+    p->grid_bin = (int)((slots + BIN_SPAN - 1) / BIN_SPAN);
     RT_CUDA(pool_alloc(&p->v.c, sizeof(Counters)));
     RT_CUDA(cudaHostAlloc(&p->h_live, sizeof(uint32_t) * POLL_SLOTS, cudaHostAllocMapped));
     RT_CUDA(cudaHostAlloc(&p->h_counters, sizeof(Counters), cudaHostAllocDefault));
@@ -763,6 +930,8 @@ int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
 #endif
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_block_defer, SHADE_BLOCK, 0));
         p->grid_shade_block = sms * std::max(occ, 1);
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_bins<true>, SHADE_BLOCK, 0));
+        p->grid_shade_bins = sms * std::max(occ, 1);
     } else {
 #if RT_EXPERIMENTS
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade, SHADE_BLOCK, 0));
@@ -770,6 +939,8 @@ int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
 #endif
         RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_block, SHADE_BLOCK, 0));
         p->grid_shade_block = sms * std::max(occ, 1);
+        RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shade_bins<false>, SHADE_BLOCK, 0));
+        p->grid_shade_bins = sms * std::max(occ, 1);
     }
     return RT_OK;
 }
@@ -824,7 +995,8 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     }
     const bool count = (st.flags & RT_RENDER_COUNTERS) != 0;
     const bool timers = (st.flags & RT_RENDER_TIMERS) != 0;
-    const bool block_shade = (st.debug_flags & RT_DEBUG_WARP_SHADE) == 0;   // the default: see the note above shade_warp_tiles
+    const bool bin_shade = (st.debug_flags & RT_DEBUG_BIN_SHADE) != 0;
+    const bool block_shade = !bin_shade && (st.debug_flags & RT_DEBUG_WARP_SHADE) == 0;   // the default: see the note above shade_warp_tiles
 
     const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
     const FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, st.debug_flags, total, npix, magic, d_accum, st.tile_index, tile_count};
@@ -862,7 +1034,10 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         } else if (count) launch_extend<true>(variant, P.grid_extend, s, ds.view, P.v, fp, cur);
         else launch_extend<false>(variant, P.grid_extend, s, ds.view, P.v, fp, cur);
         if (timed && tick() < 0) return RT_ERR_CUDA;
-        if (block_shade) {
+        if (bin_shade) {
+            if (P.suspend_below) { k_bin<true><<<P.grid_bin, BIN_THREADS, 0, s>>>(P.v, cur); k_shade_bins<true><<<P.grid_shade_bins, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur); }
+            else { k_bin<false><<<P.grid_bin, BIN_THREADS, 0, s>>>(P.v, cur); k_shade_bins<false><<<P.grid_shade_bins, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur); }
+        } else if (block_shade) {
             if (P.suspend_below) k_shade_block_defer<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
             else k_shade_block<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
         }
@@ -871,7 +1046,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         else k_shade<<<P.grid_shade, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
 #endif
         if (timed && tick() < 0) return RT_ERR_CUDA;
-        k_turnover<<<1, 1, 0, s>>>(P.v, cur, fp.total_samples, d_live + slot);
+        k_turnover<<<1, 1, 0, s>>>(P.v, cur, fp.total_samples, d_live + slot, bin_shade ? 1 : 0);
         return RT_OK;
     };
     // No per-kernel timers: GRAPH_ITERS iterations go to the GPU as ONE CUDA graph.  Small frames and the drain of
@@ -897,7 +1072,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         for (uint64_t gi = 0; !done; gi++) {
             RT_CUDA(cudaGraphLaunch(P.graph_exec, stream));
             RT_CUDA(cudaEventRecord(P.poll_ev[gi & 1], stream));
-            launches += 3 * GRAPH_ITERS; it += GRAPH_ITERS;
+            launches += (bin_shade ? 4 : 3) * GRAPH_ITERS; it += GRAPH_ITERS;
             if (gi >= 1) {   // the graph before this one: its last iteration's live count (a later one is as good: zero stays zero)
                 RT_CUDA(cudaEventSynchronize(P.poll_ev[(gi - 1) & 1]));
                 if (P.h_live[GRAPH_ITERS - 1] == 0) done = true;
@@ -909,7 +1084,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         const int rc = launch_iteration((int)(it & 1), (uint32_t)(it % POLL_SLOTS), stream, true);
         if (rc < 0) return rc;
         RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
-        launches += 3;
+        launches += bin_shade ? 4 : 3;
         if (it >= POLL_DEPTH) {
             const uint64_t old = it - POLL_DEPTH;
             RT_CUDA(cudaEventSynchronize(P.poll_ev[old % POLL_SLOTS]));
