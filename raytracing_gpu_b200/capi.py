@@ -52,7 +52,7 @@ WIDE_AUTO, WIDE_OFF, WIDE_ON = 0, 1, 2
 BUILD_TRACE = 1
 DEFER_AUTO, DEFER_OFF = 0, 1
 TRAVERSAL_FORCE = 0x100
-DEBUG_NO_GRAPH, DEBUG_RASTER_FILM, DEBUG_WARP_SHADE, DEBUG_BIN_SHADE = 1, 2, 4, 8
+DEBUG_NO_GRAPH, DEBUG_RASTER_FILM, DEBUG_WARP_SHADE, DEBUG_BLOCK_SHADE = 1, 2, 4, 8
 
 
 class MultiSettings(C.Structure):

@@ -58,6 +58,7 @@ struct __align__(128) Counters {
     struct { uint32_t n, pad[31]; } n_fin[2];     // resumed paths that finished their walk in this iteration: region [capacity, capacity + n) of pool b
     struct { uint32_t n, pad[31]; } n_dead[2];    // dead slots shade wrote into pool b (not path segments: subtracted from total_rays)
     struct { uint32_t n, pad[31]; } bin_n[8];     // class-binned shade: entries in each bin's list this iteration (k_bin)
+    struct { uint32_t n, pad[31]; } shade_done;   // blocks of k_shade_bins that have finished: the last one runs the turnover
 };
 
 struct PoolView {
@@ -554,7 +555,8 @@ __global__ void __launch_bounds__(SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(Scen
 __global__ void __launch_bounds__(SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_warp_tiles<true>(sv, pv, fp, cur); }
 #endif
 
-// The default shade: a BLOCK sorts a 256-path tile by class in shared memory (a warp shades one class), thread 0 allocates
+// Round 1's shade (RT_DEBUG_BLOCK_SHADE; the default is the class-binned pipeline below): a BLOCK sorts a 256-path tile by class
+// in shared memory (a warp shades one class, warps at class boundaries several), thread 0 allocates
 // between two barriers — five __syncthreads per tile.
 template <bool DEFER>
 __device__ __forceinline__ void shade_block_tiles(const SceneView& sv, const PoolView& pv, const FrameParams& fp, int cur) {
@@ -657,7 +659,42 @@ __device__ __forceinline__ void shade_block_tiles(const SceneView& sv, const Poo
 __global__ void __launch_bounds__(SHADE_BLOCK) k_shade_block(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_block_tiles<false>(sv, pv, fp, cur); }
 __global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_block_defer(SceneView sv, PoolView pv, FrameParams fp, int cur) { shade_block_tiles<true>(sv, pv, fp, cur); }
 
-// ---- class-binned shade (RT_DEBUG_BIN_SHADE) ----------------------------------------------------------
+// ---- turnover -------------------------------------------------------------------------------------
+// End of an iteration: totals, the next iteration's region sizes, counters back to zero, the live count to the host.
+// Run by one thread: k_turnover after the block-tile shade, the last block of k_shade_bins to finish (volatile: its L1 may
+// hold lines other blocks' atomics have moved on).
+__device__ __forceinline__ void turnover(volatile Counters* c, int cur, unsigned long long total_samples, uint32_t* live_out, bool binned) {
+    // every load first (they are independent; a store in between would serialise them), then the stores
+    uint32_t bins[NBINS];
+    #pragma unroll
+    for (int b = 0; b < NBINS; b++) bins[b] = binned ? c->bin_n[b].n : 0u;
+    const uint32_t n_b = c->n_bounce[cur], n_f = c->n_fresh[cur], n_d = c->n_dead[cur].n, n_cont = c->cont[cur].n;
+    uint32_t n_next = c->n_bounce[cur ^ 1];
+    unsigned long long cursor = c->next_sample;
+    const unsigned long long rays = c->total_rays, iter_begin = c->iter_begin;
+    if (binned) {   // k_shade_bins allocates by list index: the totals are the bin sizes
+        uint32_t goes_on = 0, ends = 0;
+        #pragma unroll
+        for (int b = 0; b < NBINS; b++) { (b < BIN_CONT ? goes_on : ends) += bins[b]; c->bin_n[b].n = 0; }
+        n_next = goes_on;
+        cursor += ends;
+        c->n_bounce[cur ^ 1] = n_next;
+        c->next_sample = cursor;
+    }
+    c->total_rays = rays + n_b + n_f - n_d;
+    c->n_bounce[cur] = 0; c->n_fresh[cur] = 0; c->n_dead[cur].n = 0;
+    const unsigned long long started = min(cursor, total_samples);   // samples regenerated by this iteration's shade
+    const uint32_t fresh_next = (uint32_t)(started - iter_begin);
+    c->n_fresh[cur ^ 1] = fresh_next;
+    c->iter_begin = started;
+    c->cur_extend = 0; c->cur_shade = 0;
+    c->cont[cur ^ 1].n = 0;       // consumed by this iteration's extend; the next iteration's extend appends to it
+    c->n_fin[cur].n = 0;
+    *live_out = n_next + fresh_next + n_cont;   // + the suspended paths the next extend resumes
+}
+__global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out) { turnover(pv.c, cur, total_samples, live_out, false); }
+
+// ---- class-binned shade (the default) -------------------------------------------------------------------
 // VERDICT r1 #3, option A: no sort and no allocation inside shade.  k_bin lists the pool positions of every class ("bin")
 // once per iteration; k_shade_bins walks the concatenation of the lists 32 entries at a time, so a warp shades paths of ONE
 // class, and because the class byte says whether a path goes on, where its result lands is a pure function of its list
@@ -721,7 +758,7 @@ __global__ void __launch_bounds__(BIN_THREADS) k_bin(PoolView pv, int cur) {
 }
 
 template <bool DEFER>
-__global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_bins(SceneView sv, PoolView pv, FrameParams fp, int cur) {
+__global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_bins(SceneView sv, PoolView pv, FrameParams fp, int cur, uint32_t* live_out) {
     __shared__ uint32_t s_work[NBINS + 1];           // work index where bin b starts (each bin padded to whole warps)
     __shared__ uint32_t s_n[NBINS], s_rank[NBINS];   // entries of bin b; entries of the bins of its group (continuing / ending) before it
     const int next = cur ^ 1;
@@ -777,38 +814,16 @@ __global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_bins(SceneView sv, Poo
         }
         w0 = __shfl_sync(0xffffffffu, w_next, 0);
     }
-}
-
-// ---- turnover -------------------------------------------------------------------------------------
-__global__ void k_turnover(PoolView pv, int cur, unsigned long long total_samples, uint32_t* live_out, int binned) {
-    Counters* c = pv.c;
-    // every load first (they are independent; a store in between would serialise them), then the stores
-    uint32_t bins[NBINS];
-    #pragma unroll
-    for (int b = 0; b < NBINS; b++) bins[b] = binned ? c->bin_n[b].n : 0u;
-    const uint32_t n_b = c->n_bounce[cur], n_f = c->n_fresh[cur], n_d = c->n_dead[cur].n, n_cont = c->cont[cur].n;
-    uint32_t n_next = c->n_bounce[cur ^ 1];
-    unsigned long long cursor = c->next_sample;
-    const unsigned long long rays = c->total_rays, iter_begin = c->iter_begin;
-    if (binned) {   // k_shade_bins allocates by list index: the totals are the bin sizes
-        uint32_t goes_on = 0, ends = 0;
-        #pragma unroll
-        for (int b = 0; b < NBINS; b++) { (b < BIN_CONT ? goes_on : ends) += bins[b]; c->bin_n[b].n = 0; }
-        n_next = goes_on;
-        cursor += ends;
-        c->n_bounce[cur ^ 1] = n_next;
-        c->next_sample = cursor;
+    // the last block to get here ends the iteration (k_turnover's job in the block-tile pipeline: one launch less)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&pv.c->shade_done.n, 1u) == gridDim.x - 1u) {
+            __threadfence();
+            pv.c->shade_done.n = 0;
+            turnover(pv.c, cur, fp.total_samples, live_out, true);
+        }
     }
-    c->total_rays = rays + n_b + n_f - n_d;
-    c->n_bounce[cur] = 0; c->n_fresh[cur] = 0; c->n_dead[cur].n = 0;
-    const unsigned long long started = min(cursor, total_samples);   // samples regenerated by this iteration's shade
-    const uint32_t fresh_next = (uint32_t)(started - iter_begin);
-    c->n_fresh[cur ^ 1] = fresh_next;
-    c->iter_begin = started;
-    c->cur_extend = 0; c->cur_shade = 0;
-    c->cont[cur ^ 1].n = 0;       // consumed by this iteration's extend; the next iteration's extend appends to it
-    c->n_fin[cur].n = 0;
-    *live_out = n_next + fresh_next + n_cont;   // + the suspended paths the next extend resumes
 }
 
 __global__ void k_scale(const float* sums, float* out, size_t n, float scale) {
@@ -995,8 +1010,8 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
     }
     const bool count = (st.flags & RT_RENDER_COUNTERS) != 0;
     const bool timers = (st.flags & RT_RENDER_TIMERS) != 0;
-    const bool bin_shade = (st.debug_flags & RT_DEBUG_BIN_SHADE) != 0;
-    const bool block_shade = !bin_shade && (st.debug_flags & RT_DEBUG_WARP_SHADE) == 0;   // the default: see the note above shade_warp_tiles
+    const bool bin_shade = (st.debug_flags & (RT_DEBUG_BLOCK_SHADE | RT_DEBUG_WARP_SHADE)) == 0;   // the default pipeline
+    const bool block_shade = (st.debug_flags & RT_DEBUG_WARP_SHADE) == 0;
 
     const unsigned long long magic = npix > 1 ? (~0ull / npix) + 1ull : 0ull;   // ceil(2^64 / npix) for npix >= 2 (exact unless npix is a power of two: the fix-up covers it)
     const FrameParams fp{st.width, st.height, st.max_depth, st.seed, s_first, st.debug_flags, total, npix, magic, d_accum, st.tile_index, tile_count};
@@ -1035,8 +1050,8 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         else launch_extend<false>(variant, P.grid_extend, s, ds.view, P.v, fp, cur);
         if (timed && tick() < 0) return RT_ERR_CUDA;
         if (bin_shade) {
-            if (P.suspend_below) { k_bin<true><<<P.grid_bin, BIN_THREADS, 0, s>>>(P.v, cur); k_shade_bins<true><<<P.grid_shade_bins, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur); }
-            else { k_bin<false><<<P.grid_bin, BIN_THREADS, 0, s>>>(P.v, cur); k_shade_bins<false><<<P.grid_shade_bins, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur); }
+            if (P.suspend_below) { k_bin<true><<<P.grid_bin, BIN_THREADS, 0, s>>>(P.v, cur); k_shade_bins<true><<<P.grid_shade_bins, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, d_live + slot); }
+            else { k_bin<false><<<P.grid_bin, BIN_THREADS, 0, s>>>(P.v, cur); k_shade_bins<false><<<P.grid_shade_bins, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur, d_live + slot); }
         } else if (block_shade) {
             if (P.suspend_below) k_shade_block_defer<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
             else k_shade_block<<<P.grid_shade_block, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
@@ -1046,7 +1061,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         else k_shade<<<P.grid_shade, SHADE_BLOCK, 0, s>>>(ds.view, P.v, fp, cur);
 #endif
         if (timed && tick() < 0) return RT_ERR_CUDA;
-        k_turnover<<<1, 1, 0, s>>>(P.v, cur, fp.total_samples, d_live + slot, bin_shade ? 1 : 0);
+        if (!bin_shade) k_turnover<<<1, 1, 0, s>>>(P.v, cur, fp.total_samples, d_live + slot);
         return RT_OK;
     };
     // No per-kernel timers: GRAPH_ITERS iterations go to the GPU as ONE CUDA graph.  Small frames and the drain of
@@ -1072,7 +1087,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         for (uint64_t gi = 0; !done; gi++) {
             RT_CUDA(cudaGraphLaunch(P.graph_exec, stream));
             RT_CUDA(cudaEventRecord(P.poll_ev[gi & 1], stream));
-            launches += (bin_shade ? 4 : 3) * GRAPH_ITERS; it += GRAPH_ITERS;
+            launches += 3 * GRAPH_ITERS; it += GRAPH_ITERS;
             if (gi >= 1) {   // the graph before this one: its last iteration's live count (a later one is as good: zero stays zero)
                 RT_CUDA(cudaEventSynchronize(P.poll_ev[(gi - 1) & 1]));
                 if (P.h_live[GRAPH_ITERS - 1] == 0) done = true;
@@ -1084,7 +1099,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         const int rc = launch_iteration((int)(it & 1), (uint32_t)(it % POLL_SLOTS), stream, true);
         if (rc < 0) return rc;
         RT_CUDA(cudaEventRecord(P.poll_ev[it % POLL_SLOTS], stream));
-        launches += bin_shade ? 4 : 3;
+        launches += 3;
         if (it >= POLL_DEPTH) {
             const uint64_t old = it - POLL_DEPTH;
             RT_CUDA(cudaEventSynchronize(P.poll_ev[old % POLL_SLOTS]));

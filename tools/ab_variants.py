@@ -60,9 +60,7 @@ print(json.dumps({"workload": desc, "prims": st.n_prims, "builder": st.builder, 
 deferred = st.n_prims >= 65536
 tag = os.path.basename(rt.lib_path()) + (" wide" if st.n_wide_nodes else " binary")
 run(f"default [{tag}]")
-run("bin_shade", debug_flags=rt.capi.DEBUG_BIN_SHADE)
-if deferred:
-    run("bin_shade+defer_off", debug_flags=rt.capi.DEBUG_BIN_SHADE, extend_defer=rt.capi.DEFER_OFF)
+run("block_shade", debug_flags=rt.capi.DEBUG_BLOCK_SHADE)
 run("warp_shade", debug_flags=rt.capi.DEBUG_WARP_SHADE)
 if os.environ.get("AB_ONLY_DEFAULT"):
     sys.exit(0)
