@@ -284,6 +284,10 @@ class Frame:
         return self.npix * self.total_spp / (ms_step * 1e-3) / 1e6
 
 
+KERNEL_MS_NOTE = ("per-kernel CUDA events of a separate pass with direct launches (no CUDA graph); shade = k_bin + k_shade_bins, "
+                  "whose last block also runs the turnover (turnover: what is left between shade's end and the next extend)")
+
+
 def short_record(fr, steps, warmup):
     """value / e2e / kernel ms of one workload (used for the per-scene `workloads` block)."""
     for _ in range(warmup):
@@ -300,7 +304,7 @@ def short_record(fr, steps, warmup):
             "e2e": fr.msamples(ms_e2e / steps), "prims": int(fr.build.n_prims), "bvh_builder": int(fr.build.builder),
             "bvh_build_ms": float(fr.build.ms_total), "commit_host_ms": float(fr.build.ms_host),
             "kernel_ms_per_step": {"extend": t.ms_extend, "shade": t.ms_shade, "generate": t.ms_generate, "turnover": t.ms_finish,
-                                   "note": "per-kernel CUDA events of a separate pass with direct launches (no CUDA graph)"}}
+                                   "note": KERNEL_MS_NOTE}}
 
 
 def main():
@@ -374,7 +378,7 @@ def main():
                 "kernel_ms_per_step": {"extend": ts.ms_extend, "shade": ts.ms_shade, "generate": ts.ms_generate, "turnover": ts.ms_finish,
                                        "total_of_this_pass": ts.ms_total,
                                        "note": "separate pass with direct launches and 3 events per iteration: sums exceed ms_per_step, "
-                                               "which is timed with 8 iterations per CUDA graph"}}
+                                               "which is timed with 8 iterations per CUDA graph; shade = k_bin + k_shade_bins (its last block runs the turnover)"}}
     # FP32 roofline (the binding one): algorithmic flops from measured traversal counters (SURVEY §8d figures) against the FMA
     # microbenchmark run on THIS GPU
     _, cstats = fr.timed(lambda: fr.step(flags=1), 1)

@@ -220,7 +220,13 @@ __device__ __forceinline__ uint8_t hit_class_of(const SceneView& sv, const Close
 constexpr int NBINS = 7, BIN_NONE = 7, BIN_CONT = 4;       // bins 0..3 continue (lambertian, metal, dielectric, isotropic), 4..6 end (light, miss, nothing to do)
 constexpr int BIN_THREADS = 1024, BIN_WARPS = BIN_THREADS / 32, BIN_ROUNDS = 8, BIN_SPAN = BIN_THREADS * BIN_ROUNDS;
 static_assert(BIN_WARPS >= 7 && BIN_ROUNDS <= 8, "one warp per bin scans; 4 bits per round in a 32-bit word");
-constexpr int BIN_CLAIM = 4;                               // rounds of 32 list entries a shading warp claims at once
+#ifndef RT_BIN_CLAIM
+#define RT_BIN_CLAIM 4
+#endif
+#ifndef RT_BINS_MIN_BLOCKS
+#define RT_BINS_MIN_BLOCKS 4
+#endif
+constexpr int BIN_CLAIM = RT_BIN_CLAIM;                    // rounds of 32 list entries a shading warp claims at once
 
 constexpr uint32_t bin_of_class(uint32_t c) {
     const uint32_t k = c & 7u;
@@ -758,7 +764,7 @@ __global__ void __launch_bounds__(BIN_THREADS) k_bin(PoolView pv, int cur) {
 }
 
 template <bool DEFER>
-__global__ void __launch_bounds__(SHADE_BLOCK, 4) k_shade_bins(SceneView sv, PoolView pv, FrameParams fp, int cur, uint32_t* live_out) {
+__global__ void __launch_bounds__(SHADE_BLOCK, RT_BINS_MIN_BLOCKS) k_shade_bins(SceneView sv, PoolView pv, FrameParams fp, int cur, uint32_t* live_out) {
     __shared__ uint32_t s_work[NBINS + 1];           // work index where bin b starts (each bin padded to whole warps)
     __shared__ uint32_t s_n[NBINS], s_rank[NBINS];   // entries of bin b; entries of the bins of its group (continuing / ending) before it
     const int next = cur ^ 1;
