@@ -218,7 +218,13 @@ __device__ __forceinline__ uint8_t hit_class_of(const SceneView& sv, const Close
 }
 
 constexpr int NBINS = 7, BIN_NONE = 7, BIN_CONT = 4;       // bins 0..3 continue (lambertian, metal, dielectric, isotropic), 4..6 end (light, miss, nothing to do)
-constexpr int BIN_THREADS = 1024, BIN_WARPS = BIN_THREADS / 32, BIN_ROUNDS = 8, BIN_SPAN = BIN_THREADS * BIN_ROUNDS;
+#ifndef RT_BIN_THREADS
+#define RT_BIN_THREADS 512
+#endif
+#ifndef RT_BIN_MIN_BLOCKS
+#define RT_BIN_MIN_BLOCKS 3
+#endif
+constexpr int BIN_THREADS = RT_BIN_THREADS, BIN_WARPS = BIN_THREADS / 32, BIN_ROUNDS = 8, BIN_SPAN = BIN_THREADS * BIN_ROUNDS;
 static_assert(BIN_WARPS >= 7 && BIN_ROUNDS <= 8, "one warp per bin scans; 4 bits per round in a 32-bit word");
 #ifndef RT_BIN_CLAIM
 #define RT_BIN_CLAIM 4
@@ -713,7 +719,7 @@ __device__ __forceinline__ uint32_t mask_of(uint32_t b0, uint32_t b1, uint32_t b
 }
 
 template <bool DEFER>
-__global__ void __launch_bounds__(BIN_THREADS) k_bin(PoolView pv, int cur) {
+__global__ void __launch_bounds__(BIN_THREADS, RT_BIN_MIN_BLOCKS) k_bin(PoolView pv, int cur) {
     __shared__ uint32_t s_cnt[8][BIN_WARPS];         // [bin][warp]: counts, then list offsets
     const uint32_t n_b = pv.c->n_bounce[cur], n_pool = n_b + pv.c->n_fresh[cur];
     const uint32_t n = n_pool + (DEFER ? pv.c->n_fin[cur].n : 0u);
