@@ -371,7 +371,10 @@ def main():
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(args.workload, {}).get("extend_dram_bytes_per_launch")
+        tj = json.load(open(tpath)).get(args.workload, {})
+        if tj.get("captured_at") == rt.lib().rt_version().decode() and "extend_dram_bytes_per_ray" in tj:
+            # ncu's DRAM bytes of one full-pool launch, per ray, x the rays of this run's average launch (drain launches are smaller)
+            traffic = tj["extend_dram_bytes_per_ray"] * ts.rays / max(ext_launches, 1)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "traffic": traffic, "kernel": extend_kernel, "peak_source": peak_src, "launches_per_step": ext_launches,
                 "avg_launch_ms": ext_ms, "share_of_step": ts.ms_extend / max(ts.ms_total, 1e-9),

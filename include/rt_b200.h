@@ -211,7 +211,8 @@ typedef struct rt_render_settings {  /* replaces render_settings (render.h:21-50
     uint32_t sample_first;           /* this call renders sample indices [sample_first, sample_first+sample_count) */
     uint32_t sample_count;           /* 0 = all */
     uint32_t flags;
-    uint32_t pool_paths;             /* wavefront pool size in paths; 0 = default */
+    uint32_t pool_paths;             /* wavefront pool size in paths; 0 = default: 32 Mi paths (4.5 GB; 16 Mi = 9.4 GB with the deferred
+                                        extend), never more than the frame has samples, halved while the GPU lacks the memory */
     uint32_t tile_index, tile_count; /* tile-split partitioning: with tile_count > 1 this call renders only the film blocks
                                         b with b % tile_count == tile_index (blocks of RT_TILE_BLOCK_PIXELS consecutive
                                         pixels in film order = 32 tiles of 8x4); the other pixels of the buffer are left
@@ -246,7 +247,8 @@ typedef struct rt_render_stats {
     uint64_t node_slots;    /* with RT_RENDER_COUNTERS: sum over warps of 32 x the longest lane's node steps, i.e. the node
                                steps the SIMD machine paid for; nodes_visited / node_slots = lane utilisation lost to rays
                                of one warp finishing at different times */
-    uint64_t reserved[3];
+    uint64_t pool_paths;    /* wavefront pool size this call used (the default halves when the GPU lacks the memory) */
+    uint64_t reserved[2];
 } rt_render_stats;
 
 /* Render into host memory: out_rgb = width*height*3 floats, linear radiance, mean over the samples rendered

@@ -29,7 +29,7 @@ class RenderStats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("ms_total", C.c_float), ("ms_generate", C.c_float),
                 ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_finish", C.c_float),
                 ("nodes_visited", C.c_uint64), ("prim_tests", C.c_uint64), ("node_slots", C.c_uint64),
-                ("reserved", C.c_uint64 * 3)]
+                ("pool_paths", C.c_uint64), ("reserved", C.c_uint64 * 2)]
 
 
 class BuildStats(C.Structure):

@@ -35,7 +35,7 @@ static int fail(int code, const char* msg) { g_err = msg; return code; }
 extern "C" {
 
 const char* rt_last_error(void) { return g_err.c_str(); }
-const char* rt_version(void) { return "rt_b200 0.2 (sm_100a)"; }
+const char* rt_version(void) { return "rt_b200 0.3 (sm_100a)"; }
 
 int rt_scene_create(rt_scene** out) {
     if (!out) return fail(RT_ERR_INVALID, "null out pointer");

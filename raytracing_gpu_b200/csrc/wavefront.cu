@@ -93,6 +93,8 @@ struct RenderPool {
     cudaGraphExec_t graph_exec = nullptr;   // GRAPH_ITERS wavefront iterations as one CUDA graph (render_impl)
     cudaStream_t capture_stream = nullptr;
     uint32_t suspend_below = 0;          // deferred extend (k_extend_defer): a full warp suspends once <= this many lanes are live; 0 = k_extend
+    uint32_t requested = 0;              // the capacity asked for when the pool was made (the default halves until the pool fits the free memory)
+    bool out_of_memory = false;          // pool_create failed on an allocation
     std::vector<cudaEvent_t> timer_ev;   // RT_RENDER_TIMERS: 3 events per iteration, reused across frames
 };
 
@@ -132,6 +134,7 @@ struct FrameParams {
 #endif
 constexpr int EXTEND_BLOCK = 128;
 constexpr uint32_t SUSPEND_MIN_PRIMS = 65536, SUSPEND_BELOW_DEFAULT = 8;
+constexpr uint32_t DEFAULT_POOL = 1u << 25, MIN_DEFAULT_POOL = 1u << 20;   // paths (render_impl)
 #ifndef EXTEND_MIN_BLOCKS
 #define EXTEND_MIN_BLOCKS 8
 #endif
@@ -913,14 +916,17 @@ int extend_occupancy(int v, int* occ) {
     return RT_OK;
 }
 
-template <class T> cudaError_t pool_alloc(T** p, size_t bytes) { return alloc_fault_due() ? cudaErrorMemoryAllocation : cudaMalloc((void**)p, bytes); }
-
 int pool_create(DeviceScene& ds, uint32_t capacity, uint32_t suspend_below) {
     RenderPool* p = new RenderPool;
     p->device = ds.device;
     p->v.capacity = capacity;
     ds.pool = p;                                  // owned by the scene from here on: a failure below is cleaned up with it
     p->suspend_below = suspend_below;
+    auto pool_alloc = [p](auto** ptr, size_t bytes) {
+        const cudaError_t e = alloc_fault_due() ? cudaErrorMemoryAllocation : cudaMalloc((void**)ptr, bytes);
+        if (e == cudaErrorMemoryAllocation) p->out_of_memory = true;
+        return e;
+    };
     const size_t slots = p->suspend_below ? 2 * (size_t)capacity : capacity;   // + the finished-resumed region at positions >= capacity
     for (int b = 0; b < 2; b++) {
         RT_CUDA(pool_alloc(&p->v.ray_o[b], sizeof(float4) * slots));
@@ -994,16 +1000,28 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         if (owned && (owned - 1) * tile_count + st.tile_index == nb - 1) npix -= nb * RT_TILE_BLOCK_PIXELS - frame_pix;
     }
     const unsigned long long total = npix * s_count;
-    // pool size: the caller's or 4 Mi paths, never more than the frame has samples, a multiple of 32, at most 2^30
-    uint32_t capacity = (uint32_t)std::min<unsigned long long>(st.pool_paths ? st.pool_paths : (1u << 22), 1ull << 30);
-    capacity = (uint32_t)std::min<unsigned long long>(capacity, std::max<unsigned long long>(total, 32ull));
-    capacity = (capacity + 31u) & ~31u;
+    // Pool size: the caller's, or DEFAULT_POOL paths (half of it with the deferred extend, whose continuation records make a path
+    // four times as big); never more than the frame has samples, a multiple of 32, at most 2^30.  The default is sized for the
+    // B200's memory, not for a cache: every iteration ends in a tail in which the longest walks run on a nearly empty GPU, and
+    // fewer, larger iterations have fewer tails (final scene 4 Mi -> 16 Mi -> 32 Mi paths: 3393 -> 3564 -> 3598 Msamples/s,
+    // 1 M-triangle mesh 4 Mi -> 16 Mi: 1069 -> 1149; profiles/r02_pool_size.md).  133 B per path: 4.5 GB (deferred: ~590 B, 9.4 GB).
     const uint32_t susp = suspend_threshold(ds, st);
-    if (ds.pool && (ds.pool->v.capacity != capacity || ds.pool->suspend_below != susp)) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
-    if (!ds.pool) {
-        const int rc = pool_create(ds, capacity, susp);
-        if (rc < 0) { render_pool_destroy(ds.pool); ds.pool = nullptr; return rc; }   // a half-built pool is never kept
+    const auto clip = [&](unsigned long long paths) {
+        uint32_t c = (uint32_t)std::min<unsigned long long>(paths, 1ull << 30);
+        c = (uint32_t)std::min<unsigned long long>(c, std::max<unsigned long long>(total, 32ull));
+        return (c + 31u) & ~31u;
+    };
+    const uint32_t requested = clip(st.pool_paths ? st.pool_paths : (susp ? DEFAULT_POOL / 2 : DEFAULT_POOL));
+    if (ds.pool && (ds.pool->requested != requested || ds.pool->suspend_below != susp)) { render_pool_destroy(ds.pool); ds.pool = nullptr; }
+    for (uint32_t c = requested; !ds.pool; c = clip(c / 2)) {
+        const int rc = pool_create(ds, c, susp);
+        if (rc == RT_OK) { ds.pool->requested = requested; break; }
+        const bool out_of_memory = ds.pool && ds.pool->out_of_memory;
+        render_pool_destroy(ds.pool); ds.pool = nullptr;                          // a half-built pool is never kept
+        if (!out_of_memory || st.pool_paths || c <= MIN_DEFAULT_POOL) return rc;   // the caller's size is the caller's choice;
+        cudaGetLastError();                                                        // the default adapts: half, down to 1 Mi paths
     }
+    const uint32_t capacity = ds.pool->v.capacity;
     RenderPool& P = *ds.pool;
     const int variant = extend_variant(ds, st);
 #if !RT_EXPERIMENTS
@@ -1135,6 +1153,7 @@ int render_impl(DeviceScene& ds, const rt_render_settings& st, float* d_accum, c
         stats->nodes_visited = c.nodes;
         stats->prim_tests = c.prim_tests;
         stats->node_slots = c.node_slots;
+        stats->pool_paths = capacity;
         if (timers) {   // per-kernel device time, summed over the iterations of this frame: 3 events per iteration + 1
             double ext = 0, shd = 0, fin = 0;
             const std::vector<cudaEvent_t>& ev = P.timer_ev;
