@@ -222,7 +222,8 @@ typedef struct rt_render_settings {  /* replaces render_settings (render.h:21-50
                                         n >= 2 = on, a warp suspends once <= n - 1 of its rays are still walking */
     uint32_t traversal;              /* 0 = the default k_extend variant; RT_TRAVERSAL_FORCE | bits selects one for A/B:
                                         1 = stack entries carry their entry distance and are culled at pop, 2 = short stack in
-                                        shared memory (trees up to 16 levels), 4 = min/max plane selection on the ALU pipe */
+                                        shared memory (trees up to 16 levels), 4 = min/max plane selection on the ALU pipe, 16 = two parked leaves per
+                                        lane with the warp's leaf tests packed into its lowest lanes (alone); all but 0 only in the experiments build */
     uint32_t debug_flags;            /* rt_debug_flags */
     uint32_t reserved[2];
 } rt_render_settings;

@@ -137,7 +137,8 @@ __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s,
 //   TV_WIDE   the 4-wide compressed tree: a step sorts up to four entered children, descends into the nearest and pushes
 //             the rest far-to-near (RT_NODE_DONE is INT_MIN = RT_WIDE_EMPTY: "no node" in both encodings)
 #define RT_SHORT_STACK 16
-enum : int { TV_PLAIN = 0, TV_TCULL = 1, TV_SMEM = 2, TV_MINMAX = 4, TV_WIDE = 8 /* walks SceneView::wide (4-wide, 8-bit boxes); plain stack only */ };
+enum : int { TV_PLAIN = 0, TV_TCULL = 1, TV_SMEM = 2, TV_MINMAX = 4, TV_WIDE = 8 /* walks SceneView::wide (4-wide, 8-bit boxes); plain stack only */,
+             TV_PACK = 16 /* two parked leaves per lane, the warp's leaf tests packed into its lowest lanes (closest_surface_packed) */ };
 
 // Closest surface hit.  A lane that reaches a leaf parks it (one register) and keeps walking; the warp enters the leaf code
 // only when some lane reaches a second leaf or nobody has nodes left, then every parked leaf is tested together (round 1:
@@ -221,6 +222,80 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
             }
             if (blocked) { parked = node; node = pop(best.t); }
             if (!__any_sync(0xffffffffu, node != RT_NODE_DONE || parked != RT_NODE_DONE)) break;
+        }
+    }
+}
+
+// TV_PACK: the leaf phase of closest_surface runs at 4-7 of 32 lanes (a lane parks ONE leaf, the phase starts when any lane meets
+// its second) and is a fifth of k_extend's instructions.  Here a lane parks up to TWO leaves and the phase hands the warp's
+// pending tests to its lowest lanes — test i runs on lane i with the owner's ray fetched by shuffles, the distance goes back the
+// same way — so a phase that starts later (a lane's THIRD leaf) tests about twice as many leaves in one pass.  Costs: t_max
+// shrinks later (more node visits), no object-space ray cache, ~30 shuffles per phase.  Same closest hit: consider() is
+// order-independent once a test made against an older t_max is re-checked against the current one.
+template <bool COUNT>
+__device__ __forceinline__ void closest_surface_packed(const SceneView& sv, const Ray& ray, float t_min, Closest& best, TraversalCounters* cnt, bool active) {
+    const SlabRay s = slab_ray(ray);
+    int node_loc[RT_STACK];
+    int sp = 0;
+    auto pop = [&]() { return sp ? node_loc[--sp] : RT_NODE_DONE; };
+    auto is_leaf = [](int n) { return n < 0 && n != RT_NODE_DONE; };
+    const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    int node = (active && sv.n_prims) ? 0 : RT_NODE_DONE;
+    int park0 = RT_NODE_DONE, park1 = RT_NODE_DONE;
+    for (;;) {
+        if (node >= 0) {
+            const NodeHit h = node_step<0>(sv.nodes + node, s, t_min, best.t);
+            if (COUNT) cnt->nodes++;
+            if (h.h0 && h.h1) {
+                const bool swap = h.t1n < h.t0n;
+                RT_DEV_ASSERT(sp < RT_STACK);
+                node_loc[sp++] = swap ? h.c0 : h.c1;
+                node = swap ? h.c1 : h.c0;
+            } else if (h.h0) node = h.c0;
+            else if (h.h1) node = h.c1;
+            else node = pop();
+            if (is_leaf(node) && park0 == RT_NODE_DONE) { park0 = node; node = pop(); }
+            if (is_leaf(node) && park1 == RT_NODE_DONE) { park1 = node; node = pop(); }
+        }
+        const bool blocked = is_leaf(node);                        // a third leaf while two are parked
+        const bool any_blocked = __any_sync(0xffffffffu, blocked), any_walking = __any_sync(0xffffffffu, node >= 0);
+        if (any_blocked || !any_walking) {
+            const uint32_t m0 = __ballot_sync(0xffffffffu, park0 != RT_NODE_DONE), m1 = __ballot_sync(0xffffffffu, park1 != RT_NODE_DONE);
+            const uint32_t n0 = __popc(m0), total = n0 + __popc(m1);
+            const uint32_t i0 = __popc(m0 & lt), i1 = n0 + __popc(m1 & lt);   // where this lane's tests sit in the packed order
+            for (uint32_t base = 0; base < total; base += 32u) {              // one pass unless more than 32 leaves are pending
+                const uint32_t i = base + lane;
+                const bool second = i >= n0, mine = i < total;
+                const uint32_t owner = mine ? __fns(second ? m1 : m0, 0u, (int)(second ? i - n0 : i) + 1) : lane;
+                const int l0 = __shfl_sync(0xffffffffu, park0, owner), l1 = __shfl_sync(0xffffffffu, park1, owner);
+                Ray r;
+                r.o.x = __shfl_sync(0xffffffffu, ray.o.x, owner); r.o.y = __shfl_sync(0xffffffffu, ray.o.y, owner); r.o.z = __shfl_sync(0xffffffffu, ray.o.z, owner);
+                r.d.x = __shfl_sync(0xffffffffu, ray.d.x, owner); r.d.y = __shfl_sync(0xffffffffu, ray.d.y, owner); r.d.z = __shfl_sync(0xffffffffu, ray.d.z, owner);
+                r.tm = __shfl_sync(0xffffffffu, ray.tm, owner);
+                const float t_max = __shfl_sync(0xffffffffu, best.t, owner);
+                float t_hit = 0.f;
+                bool hit = false;
+                if (mine) {
+                    const int prim = ~(second ? l1 : l0);
+                    RT_DEV_ASSERT((uint32_t)prim < sv.n_prims);
+                    const DPrim p = sv.prims[prim];
+                    const uint32_t chain = prim_chain(p);
+                    if (chain) r = to_object_space(sv, chain, r);
+                    if (COUNT) cnt->prim_tests++;
+                    float t;
+                    if (prim_t_local(p, r, t_min, t_max, sv.semantics, t)) { t_hit = t; hit = true; }
+                }
+                const uint32_t hits = __ballot_sync(0xffffffffu, hit);
+                const float r0 = __shfl_sync(0xffffffffu, t_hit, (i0 - base) & 31u), r1 = __shfl_sync(0xffffffffu, t_hit, (i1 - base) & 31u);
+                // a test made against the t_max of the phase's start counts only if it still is within the current one (written as the
+                // reference writes its range test, so that a NaN distance behaves as it does there)
+                if (park0 != RT_NODE_DONE && i0 - base < 32u && ((hits >> (i0 - base)) & 1u) && !(r0 > best.t)) consider(sv, ~park0, r0, best);
+                if (park1 != RT_NODE_DONE && i1 - base < 32u && ((hits >> (i1 - base)) & 1u) && !(r1 > best.t)) consider(sv, ~park1, r1, best);
+            }
+            park0 = park1 = RT_NODE_DONE;
+            if (is_leaf(node)) { park0 = node; node = pop(); }
+            if (is_leaf(node)) { park1 = node; node = pop(); }
+            if (!__any_sync(0xffffffffu, node != RT_NODE_DONE || park0 != RT_NODE_DONE)) break;
         }
     }
 }
@@ -329,7 +404,8 @@ template <bool COUNT, int V, int STRIDE, class XiOf>
 __device__ __forceinline__ Closest closest_hit(const SceneView& sv, const Ray& ray, float t_min, bool with_media, XiOf&& xi_of,
                                                TraversalCounters* cnt, bool active, int* stack_column) {
     Closest best; best.t = INFINITY; best.prim = -1;
-    closest_surface<COUNT, V, STRIDE>(sv, ray, t_min, best, cnt, active, stack_column);
+    if constexpr ((V & TV_PACK) != 0) closest_surface_packed<COUNT>(sv, ray, t_min, best, cnt, active);
+    else closest_surface<COUNT, V, STRIDE>(sv, ray, t_min, best, cnt, active, stack_column);
     if (with_media && active && sv.n_active_media) closest_medium(sv, ray, t_min, best, xi_of);
     return best;
 }

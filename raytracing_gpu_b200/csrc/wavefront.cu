@@ -875,7 +875,8 @@ uint32_t suspend_threshold(const DeviceScene& ds, const rt_render_settings& st) 
 int extend_variant(const DeviceScene& ds, const rt_render_settings& st) {
     if (ds.view.wide)   // the committed scene carries the 4-wide compressed tree (A/B: entry-distance culling of its stack entries)
         return TV_WIDE | (((st.traversal & RT_TRAVERSAL_FORCE) && RT_EXPERIMENTS) ? (int)(st.traversal & TV_TCULL) : 0);
-    int v = (st.traversal & RT_TRAVERSAL_FORCE) ? (int)(st.traversal & 7u) : (int)RT_TRAVERSAL_DEFAULT_BITS;
+    int v = (st.traversal & RT_TRAVERSAL_FORCE) ? (int)(st.traversal & 23u) : (int)RT_TRAVERSAL_DEFAULT_BITS;
+    if (v & TV_PACK) v = TV_PACK;
     if (ds.build.bvh_depth == 0 || ds.build.bvh_depth + 1 > RT_SHORT_STACK) v &= ~TV_SMEM;
     return v;
 }
@@ -894,6 +895,7 @@ template <bool COUNT> void launch_extend(int v, int grid, cudaStream_t s, const 
     case 6: k_extend<COUNT, 6><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 7: k_extend<COUNT, 7><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     case 9: k_extend<COUNT, 9><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
+    case 16: k_extend<COUNT, 16><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
 #endif
     default: k_extend<COUNT, TV_WIDE><<<grid, EXTEND_BLOCK, 0, s>>>(sv, pv, fp, cur); break;
     }
@@ -910,6 +912,7 @@ int extend_occupancy(int v, int* occ) {
     case 6: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 6>, EXTEND_BLOCK, 0)); break;
     case 7: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 7>, EXTEND_BLOCK, 0)); break;
     case 9: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 9>, EXTEND_BLOCK, 0)); break;
+    case 16: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, 16>, EXTEND_BLOCK, 0)); break;
 #endif
     default: RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_extend<false, TV_WIDE>, EXTEND_BLOCK, 0)); break;
     }

@@ -61,6 +61,8 @@ deferred = st.n_prims >= 65536
 tag = os.path.basename(rt.lib_path()) + (" wide" if st.n_wide_nodes else " binary")
 run(f"default [{tag}]")
 run("block_shade", debug_flags=rt.capi.DEBUG_BLOCK_SHADE)
+if not deferred:
+    run("pack_leaves", traversal=F | 16)
 run("warp_shade", debug_flags=rt.capi.DEBUG_WARP_SHADE)
 if os.environ.get("AB_ONLY_DEFAULT"):
     sys.exit(0)
