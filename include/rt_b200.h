@@ -234,7 +234,8 @@ enum rt_debug_flags {
     RT_DEBUG_RASTER_FILM = 2,  /* samples walk the film row by row instead of in 8x4 tiles */
     RT_DEBUG_WARP_SHADE = 4,   /* the barrier-free warp-tile shade kernel (measured slower than the block-tile default: A/B only) */
     RT_DEBUG_BLOCK_SHADE = 8   /* round 1's block-tile shade (a block sorts 256 paths by class, allocates with atomics, separate k_turnover) instead of
-                                  the class-binned pipeline k_bin + k_shade_bins: A/B, and 4 % faster on frames as small as BASELINE config 1 */
+                                  the class-binned pipeline k_bin + k_shade_bins: an independent implementation of the same function, kept
+                                  for A/B and as a cross-check in the tests (4-12 % slower on every BASELINE configuration) */
 };
 
 typedef struct rt_render_stats {

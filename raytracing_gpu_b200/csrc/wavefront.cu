@@ -151,6 +151,18 @@ __device__ __forceinline__ uint32_t warp_claim(uint32_t* cursor, uint32_t n = 32
     return __shfl_sync(0xffffffffu, base, 0);
 }
 
+// The same with the FIRST claim of every warp fixed by its position in the grid: the counter only hands out what lies behind the
+// grid's first sweep.  A launch over a nearly empty pool (the drain of every frame, every iteration of a small one) then ends
+// without a single atomic, instead of one per warp on one address (4736 of them: the 6 us floor of k_extend).
+struct WarpClaim {
+    uint32_t* cursor; uint32_t n, sweep; bool first;
+    __device__ __forceinline__ WarpClaim(uint32_t* c, uint32_t n_) : cursor(c), n(n_), sweep(n_ * (gridDim.x * (blockDim.x >> 5))), first(true) {}
+    __device__ __forceinline__ uint32_t next() {
+        if (first) { first = false; return n * (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)); }
+        return sweep + warp_claim(cursor, n);
+    }
+};
+
 // g -> (pixel, sample): g = sample * npix + pixel.  Division by the frame size through a precomputed 64-bit
 // reciprocal (one mul.hi + a fix-up) instead of a 64-bit divide per path.
 __device__ __forceinline__ void split_sample_index(const FrameParams& fp, unsigned long long g, uint32_t& pixel, uint32_t& sample) {
@@ -263,8 +275,9 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, EXTEND_MIN_BLOCKS) k_extend(Scen
     const float4* thr = pv.thr[cur];
     TraversalCounters tc{0, 0};
     unsigned long long slots = 0;
+    WarpClaim claim(&pv.c->cur_extend, 32u);
     for (;;) {
-        const uint32_t base = warp_claim(&pv.c->cur_extend);
+        const uint32_t base = claim.next();
         if (base >= n) break;
         const uint32_t idx = base + lane;
         const bool in_range = idx < n;              // closest_hit is warp-collective
@@ -316,8 +329,9 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
     TraversalCounters tc{0, 0};
     uint32_t steps = 0;
     int stack[RT_STACK];
+    WarpClaim claim(&pv.c->cur_extend, 32u);
     for (;;) {
-        const uint32_t base = warp_claim(&pv.c->cur_extend);
+        const uint32_t base = claim.next();
         if (base >= n) break;
         const bool resumed = base < n_c32;                       // warp-uniform
         const uint32_t idx = (resumed ? base : base - n_c32) + lane;
@@ -777,28 +791,34 @@ __global__ void __launch_bounds__(SHADE_BLOCK, RT_BINS_MIN_BLOCKS) k_shade_bins(
     __shared__ uint32_t s_work[NBINS + 1];           // work index where bin b starts (each bin padded to whole warps)
     __shared__ uint32_t s_n[NBINS], s_rank[NBINS];   // entries of bin b; entries of the bins of its group (continuing / ending) before it
     const int next = cur ^ 1;
-    if (threadIdx.x == 0) {
-        uint32_t w = 0, rc = 0, rt = 0;
-        for (int b = 0; b < NBINS; b++) {
-            const uint32_t nb = pv.c->bin_n[b].n;
-            s_work[b] = w; s_n[b] = nb;
-            w += (nb + 31u) & ~31u;
-            if (b < BIN_CONT) { s_rank[b] = rc; rc += nb; } else { s_rank[b] = rt; rt += nb; }
+    const uint32_t lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) {   // lane b < NBINS owns bin b: one load latency for all counters, offsets by warp scans
+        const uint32_t nb = lane < (uint32_t)NBINS ? pv.c->bin_n[lane].n : 0u;
+        const uint32_t padded = (nb + 31u) & ~31u;
+        uint32_t w = padded, rc = lane < (uint32_t)BIN_CONT ? nb : 0u, rt = lane < (uint32_t)BIN_CONT ? 0u : nb;
+        #pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            const uint32_t yw = __shfl_up_sync(0xffffffffu, w, o), yc = __shfl_up_sync(0xffffffffu, rc, o), yt = __shfl_up_sync(0xffffffffu, rt, o);
+            if ((int)lane >= o) { w += yw; rc += yc; rt += yt; }
         }
-        s_work[NBINS] = w;
+        if (lane < (uint32_t)NBINS) { s_work[lane] = w - padded; s_n[lane] = nb; s_rank[lane] = (lane < (uint32_t)BIN_CONT ? rc : rt) - nb; }
+        if (lane == (uint32_t)NBINS - 1u) s_work[NBINS] = w;
     }
-    __syncthreads();                                  // the only barrier: once per block
+    __syncthreads();                                  // the only barrier before the block's work: once per block
     const uint32_t n_work = s_work[NBINS];
     const uint32_t n_end = s_rank[NBINS - 1] + s_n[NBINS - 1];
-    const unsigned long long g_first = pv.c->next_sample;     // no shade warp moves the cursor: k_turnover adds n_end
+    const unsigned long long g_first = pv.c->next_sample;     // no shade warp moves the cursor: the turnover adds n_end
     const uint32_t n_regen = g_first < fp.total_samples ? (uint32_t)min((unsigned long long)n_end, fp.total_samples - g_first) : 0u;
-    const uint32_t lane = threadIdx.x & 31;
-    uint32_t w0 = warp_claim(&pv.c->cur_shade, 32u * BIN_CLAIM);
+    // a warp claims BIN_CLAIM rounds at a time when there is enough work to keep every warp of the grid busy that way, else one
+    // (mid-size iterations: 100 k paths are 3 k rounds for 4.7 k warps); the first claim is fixed by the warp's place in the grid
+    const uint32_t grid_warps = gridDim.x * (SHADE_BLOCK / 32);
+    const uint32_t rounds = n_work >= 32u * BIN_CLAIM * grid_warps ? (uint32_t)BIN_CLAIM : 1u;
+    uint32_t w0 = 32u * rounds * (blockIdx.x * (SHADE_BLOCK / 32) + (threadIdx.x >> 5));
     while (w0 < n_work) {
         uint32_t w_next = 0;
-        if (lane == 0) w_next = atomicAdd(&pv.c->cur_shade, 32u * BIN_CLAIM);   // in flight while this claim is shaded
+        if (lane == 0) w_next = 32u * rounds * grid_warps + atomicAdd(&pv.c->cur_shade, 32u * rounds);   // in flight while this claim is shaded
         #pragma unroll 1
-        for (int r = 0; r < BIN_CLAIM; r++) {
+        for (uint32_t r = 0; r < rounds; r++) {
             const uint32_t w = w0 + 32u * r;
             if (w >= n_work) break;
             uint32_t b = 0;
