@@ -897,14 +897,24 @@ __global__ void __launch_bounds__(128) k_wide_level(const BNode* __restrict__ no
         float inv[3];
         const float ext[3] = {u.hx - u.lx, u.hy - u.ly, u.hz - u.lz};
         for (int a = 0; a < 3; a++) {
+#if RT_WIDE_FOLD
+            const float step = fmaxf(ext[a], 1e-30f) * (1.0f / 253.0f) * 1.0000002f;     // the grid starts one step below the box: planes at 1 .. 254
+#else
             const float step = fmaxf(ext[a], 1e-30f) * (1.0f / 255.0f) * 1.0000002f;     // a hair more than extent / 255
+#endif
             uint32_t e = (__float_as_uint(step) >> 23) & 0xffu;
             if (__float_as_uint(step) & 0x7fffffu) e++;                                   // round the step up to a power of two
             e = min(max(e, 1u), 254u);
             eb[a] = e;
             inv[a] = __uint_as_float((254u - e) << 23);                                   // 2^-(e - 127), exact
         }
+#if RT_WIDE_FOLD
+        const float org[3] = {__fsub_rd(u.lx, __uint_as_float(eb[0] << 23)), __fsub_rd(u.ly, __uint_as_float(eb[1] << 23)), __fsub_rd(u.lz, __uint_as_float(eb[2] << 23))};
+        const float guard = 1.0f / 128.0f;     // of a step, on both sides of every plane: covers the folded plane arithmetic of wide_step
+#else
         const float org[3] = {u.lx, u.ly, u.lz};
+        const float guard = 0.f;
+#endif
         uint32_t ql[3] = {0, 0, 0}, qh[3] = {0, 0, 0};
         int cnt_internal = 0;
         for (int c = 0; c < 4; c++) {
@@ -912,7 +922,7 @@ __global__ void __launch_bounds__(128) k_wide_level(const BNode* __restrict__ no
             if (c < n) {
                 const float lo[3] = {box[c].lx, box[c].ly, box[c].lz}, hi[3] = {box[c].hx, box[c].hy, box[c].hz}, o[3] = {org[0], org[1], org[2]};
                 for (int a = 0; a < 3; a++) {
-                    const float fl = floorf(__fmul_rd(__fsub_rd(lo[a], o[a]), inv[a])), fh = ceilf(__fmul_ru(__fsub_ru(hi[a], o[a]), inv[a]));
+                    const float fl = floorf(__fmul_rd(__fsub_rd(lo[a], o[a]), inv[a]) - guard), fh = ceilf(__fmul_ru(__fsub_ru(hi[a], o[a]), inv[a]) + guard);
                     l[a] = (uint32_t)fminf(fmaxf(fl, 0.f), 255.f);
                     h[a] = (uint32_t)fminf(fmaxf(fh, 0.f), 255.f);
                 }

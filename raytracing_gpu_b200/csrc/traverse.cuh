@@ -89,6 +89,9 @@ __device__ __forceinline__ NodeHit node_step(const BNode* np, const SlabRay& s, 
 // are sorted by entry distance (misses last) with a five-comparator network.  Measured and not adopted on the 1 M-triangle
 // mesh (profiles/r02_wide_nodes.md): folding the 2^23 into the plane offset (saves 24 FADD, but the builder must pad every box
 // by a quantisation step: +7 % node visits, extend +1.8 %), and sorting only the nearest child to the front (+1 % visits, +0.8 %).
+#ifndef RT_WIDE_FOLD
+#define RT_WIDE_FOLD 0
+#endif
 struct WideHits { float t[4]; int c[4]; };   // ascending entry distance; a miss is (+inf, RT_NODE_DONE)
 __device__ __forceinline__ float byte_to_float(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f; }
 __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s, float t_min, float t_max) {
@@ -104,11 +107,25 @@ __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s,
     const uint32_t nz = pz ? w2.z : w3.y, fz = pz ? w3.y : w2.z;                      // qlo_z / qhi_z
     const int code[4] = {(int)w1.x, (int)w1.y, (int)w1.z, (int)w1.w};
     WideHits h;
+#if RT_WIDE_FOLD
+    // plane byte q as the float 1 + q * 2^-15 (one PRMT into the mantissa of 1.0): t = (1 + q 2^-15) * (2^15 s) + (b - 2^15 s), one
+    // FMA and no subtraction per plane.  The offset b - 2^15 s is rounded: an error of up to 1/512 of a quantisation step, which the
+    // builder's 1/128-step guard band around every plane covers (bvh_build.cu, RT_WIDE_FOLD)
+    const float kx = sx * 32768.0f, ky = sy * 32768.0f, kz = sz * 32768.0f;
+    const float cx = bx - kx, cy = by - ky, cz = bz - kz;
+    #define RT_WPLANE(w, sel, k, c) fmaf(__uint_as_float(__byte_perm(w, 0x3F800000u, sel)), k, c)
+    #pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint32_t sel = 0x7604u | ((uint32_t)c << 4);
+        const float tn = fmaxf(fmaxf(RT_WPLANE(nx, sel, kx, cx), RT_WPLANE(ny, sel, ky, cy)), fmaxf(RT_WPLANE(nz, sel, kz, cz), t_min));
+        const float tf = fminf(fminf(RT_WPLANE(fx, sel, kx, cx), RT_WPLANE(fy, sel, ky, cy)), fminf(RT_WPLANE(fz, sel, kz, cz), t_max));
+#else
     #pragma unroll
     for (int c = 0; c < 4; c++) {
         const uint32_t sel = 0x7540u | (uint32_t)c;
         const float tn = fmaxf(fmaxf(fmaf(byte_to_float(nx, sel), sx, bx), fmaf(byte_to_float(ny, sel), sy, by)), fmaxf(fmaf(byte_to_float(nz, sel), sz, bz), t_min));
         const float tf = fminf(fminf(fmaf(byte_to_float(fx, sel), sx, bx), fmaf(byte_to_float(fy, sel), sy, by)), fminf(fmaf(byte_to_float(fz, sel), sz, bz), t_max));
+#endif
         const bool hit = tn <= tf && code[c] != RT_WIDE_EMPTY;
         h.t[c] = hit ? tn : INFINITY;
         h.c[c] = hit ? code[c] : RT_NODE_DONE;
