@@ -56,6 +56,11 @@ struct __align__(16) BNode {
 };
 static_assert(sizeof(BNode) == 64, "BNode must be 64 bytes");
 
+// wide_step's plane arithmetic and the builder's quantisation must agree (traverse.cuh, bvh_build.cu): 1 = folded planes + guard band
+#ifndef RT_WIDE_FOLD
+#define RT_WIDE_FOLD 1
+#endif
+
 // 4-wide BVH node with 8-bit child boxes (north_star (1): "wide-node SoA layout with quantised child AABBs and 128-bit
 // vectorised node loads"): 64 bytes = four 128-bit loads decide FOUR descents (BNode: two).  A child's box is
 // origin + q * 2^exp per axis, q in 0..255, rounded outwards; the planes are stored SoA (one 32-bit word holds the four

@@ -86,12 +86,11 @@ __device__ __forceinline__ NodeHit node_step(const BNode* np, const SlabRay& s, 
 // Per node: three scales 2^e and the three offsets (origin - ray origin) / d, then per child and axis one byte -> float
 // (PRMT into the mantissa of 2^23, minus 2^23: exact) and one FMA per plane.  Near / far planes are chosen for all four
 // children at once by swapping the packed lo / hi words of an axis when the direction is negative.  The four candidates
-// are sorted by entry distance (misses last) with a five-comparator network.  Measured and not adopted on the 1 M-triangle
-// mesh (profiles/r02_wide_nodes.md): folding the 2^23 into the plane offset (saves 24 FADD, but the builder must pad every box
-// by a quantisation step: +7 % node visits, extend +1.8 %), and sorting only the nearest child to the front (+1 % visits, +0.8 %).
-#ifndef RT_WIDE_FOLD
-#define RT_WIDE_FOLD 0
-#endif
+// are sorted by entry distance (misses last) with a five-comparator network.  RT_WIDE_FOLD (default): the byte goes into the
+// mantissa of 1.0 instead (1 + q 2^-15) and the subtraction is folded into the plane offset — 21 instructions fewer per step, an
+// extra error of <= 1/512 step that a 1/128-step guard band in the builder covers: +0.4 % node visits, extend -2.4 %, mesh +2 %.
+// Measured and not adopted (profiles/r02_wide_nodes.md): the same fold through 2^23 (error of half a step: the builder must pad
+// every box by a whole step, +7 % node visits, extend +1.8 %), and sorting only the nearest child to the front (+1 % visits, +0.8 %).
 struct WideHits { float t[4]; int c[4]; };   // ascending entry distance; a miss is (+inf, RT_NODE_DONE)
 __device__ __forceinline__ float byte_to_float(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)) - 8388608.0f; }
 __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s, float t_min, float t_max) {
