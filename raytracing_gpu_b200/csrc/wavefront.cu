@@ -135,8 +135,11 @@ struct FrameParams {
 constexpr int EXTEND_BLOCK = 128;
 constexpr uint32_t SUSPEND_MIN_PRIMS = 65536, SUSPEND_BELOW_DEFAULT = 8;
 constexpr uint32_t DEFAULT_POOL = 1u << 25, MIN_DEFAULT_POOL = 1u << 20;   // paths (render_impl)
+// blocks of k_extend per SM: 9 x 128 threads = 36 warps at 56 registers.  Same-box A/B on the final scene / 1 M-triangle mesh
+// (profiles/r02_traversal_ab.md): 6 (77 registers, no spills) -8 % / -8 %, 7 -5 % / -3 %, 8 (64 registers) 0, 9 +3.0 % / +2.7 %,
+// 10 (48 registers, 220 B of spill loads) -5 % / -4 %: occupancy pays until the spills reach the node loop
 #ifndef EXTEND_MIN_BLOCKS
-#define EXTEND_MIN_BLOCKS 8
+#define EXTEND_MIN_BLOCKS 9
 #endif
 
 // work index -> pool position: bounced paths first, fresh camera paths at the top end of the pool
