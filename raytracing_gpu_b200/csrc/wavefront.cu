@@ -471,7 +471,10 @@ __device__ __forceinline__ bool shade_path(const SceneView& sv, const PoolView& 
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 4
 #endif
-constexpr int SHADE_BLOCK = 256, SHADE_WARPS = SHADE_BLOCK / 32;
+#ifndef RT_SHADE_BLOCK
+#define RT_SHADE_BLOCK 256
+#endif
+constexpr int SHADE_BLOCK = RT_SHADE_BLOCK, SHADE_WARPS = SHADE_BLOCK / 32;
 constexpr int WTILE = RT_WTILE, WROUNDS = WTILE / 32;       // paths per warp tile / rounds of 32
 
 // Warp-tile shade (RT_DEBUG_WARP_SHADE): round 2's attempt to remove the block-wide barriers of the block-tile kernel below
