@@ -38,6 +38,13 @@ enum rt_status {
 const char* rt_last_error(void);
 const char* rt_version(void);
 
+/* sizeof() of a public struct as this library was compiled (no counterpart in the reference): lets a binding that mirrors the
+ * structs by hand (ctypes, cgo, JNI) check its layout at load time instead of corrupting memory.  Unknown id: 0. */
+enum rt_struct_id { RT_STRUCT_RENDER_SETTINGS = 0, RT_STRUCT_RENDER_STATS = 1, RT_STRUCT_BUILD_SETTINGS = 2, RT_STRUCT_BUILD_STATS = 3,
+                    RT_STRUCT_MULTI_SETTINGS = 4, RT_STRUCT_MULTI_STATS = 5, RT_STRUCT_DRAW_SETTINGS = 6, RT_STRUCT_CHECKPOINT_INFO = 7,
+                    RT_STRUCT_CATALOG_PARAMS = 8 };
+size_t rt_struct_size(int rt_struct_id);
+
 /* ---- scene lifetime: replaces struct scene's ctor/dtor (scenes.h:36-67) ---- */
 int rt_scene_create(rt_scene** out);
 void rt_scene_destroy(rt_scene* s);

@@ -105,7 +105,7 @@ def lib():
     L = C.CDLL(path)
     vp, i32, f32, u32p = C.c_void_p, C.c_int, C.c_float, C.POINTER(C.c_uint32)
     sig = {
-        "rt_last_error": (C.c_char_p, []), "rt_version": (C.c_char_p, []),
+        "rt_last_error": (C.c_char_p, []), "rt_version": (C.c_char_p, []), "rt_struct_size": (C.c_size_t, [i32]),
         "rt_scene_create": (i32, [C.POINTER(vp)]), "rt_scene_destroy": (None, [vp]),
         "rt_tex_solid": (i32, [vp, f32, f32, f32]), "rt_tex_checker": (i32, [vp, i32, i32]),
         "rt_perlin_tables": (i32, [vp, vp, vp]), "rt_tex_noise": (i32, [vp, i32, f32]),
@@ -153,11 +153,17 @@ def lib():
     for name, (res, args) in sig.items():
         fn = getattr(L, name)      # AttributeError here means the .so does not export a declared symbol
         fn.restype, fn.argtypes = res, args
+    # the structs above are mirrored by hand: refuse a library whose layout differs (include/rt_b200.h, rt_struct_id)
+    for sid, cls in enumerate(STRUCT_MIRRORS):
+        if L.rt_struct_size(sid) != C.sizeof(cls):
+            raise RtError(f"{path}: sizeof({cls.__name__}) is {L.rt_struct_size(sid)} in the library, {C.sizeof(cls)} in this binding")
     _lib = L
     return L
 
 
 EXPORTED_SYMBOLS = None  # filled lazily by tests from include/rt_b200.h
+# in the order of enum rt_struct_id
+STRUCT_MIRRORS = (RenderSettings, RenderStats, BuildSettings, BuildStats, MultiSettings, MultiStats, DrawSettings, CheckpointInfo, CatalogParams)
 
 
 def _f32(a):

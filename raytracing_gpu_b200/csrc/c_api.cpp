@@ -2,6 +2,8 @@
 // The device-side entry points (commit / first_hit / render) live in device_api.cu.
 #include "scene_host.h"
 #include "device_scene.h"
+#include "../../include/rt_catalog.h"
+#include "../../include/rt_output.h"
 
 #include <algorithm>
 #include <cmath>
@@ -36,6 +38,21 @@ extern "C" {
 
 const char* rt_last_error(void) { return g_err.c_str(); }
 const char* rt_version(void) { return "rt_b200 0.3 (sm_100a)"; }
+
+size_t rt_struct_size(int id) {
+    switch (id) {
+    case RT_STRUCT_RENDER_SETTINGS: return sizeof(rt_render_settings);
+    case RT_STRUCT_RENDER_STATS: return sizeof(rt_render_stats);
+    case RT_STRUCT_BUILD_SETTINGS: return sizeof(rt_build_settings);
+    case RT_STRUCT_BUILD_STATS: return sizeof(rt_build_stats);
+    case RT_STRUCT_MULTI_SETTINGS: return sizeof(rt_multi_settings);
+    case RT_STRUCT_MULTI_STATS: return sizeof(rt_multi_stats);
+    case RT_STRUCT_DRAW_SETTINGS: return sizeof(rt_draw_settings);
+    case RT_STRUCT_CHECKPOINT_INFO: return sizeof(rt_checkpoint_info);
+    case RT_STRUCT_CATALOG_PARAMS: return sizeof(rt_catalog_params);
+    default: return 0;
+    }
+}
 
 int rt_scene_create(rt_scene** out) {
     if (!out) return fail(RT_ERR_INVALID, "null out pointer");

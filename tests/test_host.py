@@ -190,3 +190,14 @@ def test_commit_without_gpu_fails_loudly():
     s = rt.Scene(); s.replay(g["program"])
     with pytest.raises(rt.RtError, match="CUDA"):
         s.commit(0)
+
+
+def test_struct_layouts_of_the_binding_match_the_library():
+    """rt_struct_size (include/rt_b200.h): every struct the ctypes binding mirrors by hand has the size the library was compiled
+    with; an unknown id answers 0.  (The binding performs the same check when it loads the library.)"""
+    import ctypes as C
+    L = rt.lib()
+    assert len(rt.capi.STRUCT_MIRRORS) == 9
+    for sid, cls in enumerate(rt.capi.STRUCT_MIRRORS):
+        assert L.rt_struct_size(sid) == C.sizeof(cls) > 0, cls.__name__
+    assert L.rt_struct_size(9) == 0 and L.rt_struct_size(-1) == 0
