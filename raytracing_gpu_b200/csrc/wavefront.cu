@@ -133,7 +133,7 @@ struct FrameParams {
 #define RT_EXPERIMENTS 0
 #endif
 constexpr int EXTEND_BLOCK = 128;
-constexpr uint32_t SUSPEND_MIN_PRIMS = 65536, SUSPEND_BELOW_DEFAULT = 8;
+constexpr uint32_t SUSPEND_MIN_PRIMS = 65536, SUSPEND_BELOW_DEFAULT = 12;   // re-swept on the v18 pipeline: 4 / 8 / 12 / 16 / 20 = 120.5 / 115.5 / 114.4 / 116.7 / 122.8 ms
 constexpr uint32_t DEFAULT_POOL = 1u << 25, MIN_DEFAULT_POOL = 1u << 20;   // paths (render_impl)
 // blocks of k_extend per SM: 9 x 128 threads = 36 warps at 56 registers.  Same-box A/B on the final scene / 1 M-triangle mesh
 // (profiles/r02_traversal_ab.md): 6 (77 registers, no spills) -8 % / -8 %, 7 -5 % / -3 %, 8 (64 registers) 0, 9 +3.0 % / +2.7 %,
