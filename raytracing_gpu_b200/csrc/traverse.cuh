@@ -153,6 +153,10 @@ __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s,
 //   TV_WIDE   the 4-wide compressed tree: a step sorts up to four entered children, descends into the nearest and pushes
 //             the rest far-to-near (RT_NODE_DONE is INT_MIN = RT_WIDE_EMPTY: "no node" in both encodings)
 #define RT_SHORT_STACK 16
+#ifndef RT_STEP_UNROLL
+#define RT_STEP_UNROLL 2   // node steps between two looks at the leaf-phase condition (two votes + a branch per look): 1 / 2 / 3 / 4 =
+                           // final scene 74.99 / 72.83 / 73.09 / 72.58 ms, mesh 114.5 / 111.3 / 116.1 / 121.1 (profiles/r02_traversal_ab.md)
+#endif
 enum : int { TV_PLAIN = 0, TV_TCULL = 1, TV_SMEM = 2, TV_MINMAX = 4, TV_WIDE = 8 /* walks SceneView::wide (4-wide, 8-bit boxes); plain stack only */,
              TV_PACK = 16 /* two parked leaves per lane, the warp's leaf tests packed into its lowest lanes (closest_surface_packed) */ };
 
@@ -199,6 +203,8 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     int node = (active && sv.n_prims) ? 0 : RT_NODE_DONE;
     int parked = RT_NODE_DONE;
     for (;;) {
+        #pragma unroll
+        for (int unrolled = 0; unrolled < RT_STEP_UNROLL; unrolled++)
         if (node >= 0) {
             if constexpr ((V & TV_WIDE) != 0) {
                 const WideHits h = wide_step(sv.wide + node, s, t_min, best.t);
@@ -337,6 +343,8 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
     int node = w.node, parked = w.parked, sp = w.sp;
     auto pop = [&]() { return sp ? stack[--sp] : RT_NODE_DONE; };
     for (;;) {
+        #pragma unroll
+        for (int unrolled = 0; unrolled < RT_STEP_UNROLL; unrolled++)
         if (node >= 0) {
             if constexpr (WIDE) {
                 const WideHits h = wide_step(sv.wide + node, s, t_min, best.t);
@@ -362,7 +370,7 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
         }
         const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
         const bool any_blocked = __any_sync(0xffffffffu, blocked), any_walking = __any_sync(0xffffffffu, node >= 0);
-        if (COUNT) (*steps)++;
+        if (COUNT) (*steps) += RT_STEP_UNROLL;
         if (any_blocked || !any_walking) {
             if (parked != RT_NODE_DONE) {
                 const int prim = ~parked;
