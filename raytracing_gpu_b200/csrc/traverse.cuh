@@ -9,7 +9,7 @@
 
 namespace rtb {
 
-#define RT_STACK RT_STACK_DEPTH   // Karras depth bound: 63 key bits + index bits for duplicate keys; PLOC depth is checked at build
+#define RT_STACK (RT_STACK_DEPTH + 1)   // + the sentinel entry; Karras depth bound: 63 key bits + index bits for duplicate keys; PLOC depth is checked at build
 
 struct Closest {
     float t;     // +inf on miss
@@ -153,6 +153,9 @@ __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s,
 //   TV_WIDE   the 4-wide compressed tree: a step sorts up to four entered children, descends into the nearest and pushes
 //             the rest far-to-near (RT_NODE_DONE is INT_MIN = RT_WIDE_EMPTY: "no node" in both encodings)
 #define RT_SHORT_STACK 16
+#ifndef RT_STACK_SENTINEL
+#define RT_STACK_SENTINEL 1   // final scene +1.4 %, big_scene1 +1.9 % (profiles/r02_traversal_ab.md)
+#endif
 #ifndef RT_STEP_UNROLL
 #define RT_STEP_UNROLL 2   // node steps between two looks at the leaf-phase condition (two votes + a branch per look): 1 / 2 / 3 / 4 =
                            // final scene 74.99 / 72.83 / 73.09 / 72.58 ms, mesh 114.5 / 111.3 / 116.1 / 121.1 (profiles/r02_traversal_ab.md)
@@ -176,6 +179,11 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     int node_loc[SM ? 1 : RT_STACK];                    // local-memory stack (only the arrays: sp stays a register)
     float tn_loc[(SM || !TC) ? 1 : RT_STACK];
     int sp = 0;
+#if RT_STACK_SENTINEL
+    // entry 0 is a sentinel "no node": a pop never has to ask whether the stack is empty (a lane that pops the sentinel is done and
+    // never pops again)
+    if constexpr (!TC && !SM) { node_loc[0] = RT_NODE_DONE; sp = 1; }
+#endif
     // shared-memory column of this thread: node words, then RT_SHORT_STACK rows further the entry distances (TC)
     auto push = [&](int n, float tn) {
         RT_DEV_ASSERT(sp < (SM ? RT_SHORT_STACK : RT_STACK));
@@ -186,6 +194,9 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
     };
     auto pop = [&](float t_max) {
         if constexpr (!TC) {
+#if RT_STACK_SENTINEL
+            if constexpr (!SM) { RT_DEV_ASSERT(sp > 0); sp--; return node_loc[sp]; }
+#endif
             if (!sp) return RT_NODE_DONE;
             sp--;
             if constexpr (SM) return stack_column[sp * STRIDE]; else return node_loc[sp];
@@ -341,7 +352,11 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
     uint32_t cached_chain = 0;
     Ray cached = ray;
     int node = w.node, parked = w.parked, sp = w.sp;
+#if RT_STACK_SENTINEL
+    auto pop = [&]() { RT_DEV_ASSERT(sp > 0); return stack[--sp]; };   // stack[0] is the caller's sentinel RT_NODE_DONE (see closest_surface)
+#else
     auto pop = [&]() { return sp ? stack[--sp] : RT_NODE_DONE; };
+#endif
     for (;;) {
         #pragma unroll
         for (int unrolled = 0; unrolled < RT_STEP_UNROLL; unrolled++)

@@ -359,6 +359,9 @@ __global__ void __launch_bounds__(EXTEND_BLOCK, DEFER_MIN_BLOCKS) k_extend_defer
             o = pv.ray_o[cur][pos]; d = pv.ray_d[cur][pos];
             dead = (__float_as_uint(d.w) >> 24) == DEAD_BOUNCE;
             if (active && !dead && sv.n_prims) w.node = 0;
+#if RT_STACK_SENTINEL
+            stack[0] = RT_NODE_DONE; w.sp = 1;   // a fresh walk starts on the sentinel; a resumed one brings it along in its record
+#endif
         }
         Ray r; r.o = make_float3(o.x, o.y, o.z); r.d = make_float3(d.x, d.y, d.z); r.tm = o.w;
         // only whole batches suspend: a few stragglers left over at the end of a list would otherwise advance a leaf phase per iteration
