@@ -156,9 +156,6 @@ __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s,
 #ifndef RT_STACK_SENTINEL
 #define RT_STACK_SENTINEL 1   // final scene +1.4 %, big_scene1 +1.9 % (profiles/r02_traversal_ab.md)
 #endif
-#ifndef RT_PHASE_MIN_BLOCKED
-#define RT_PHASE_MIN_BLOCKED 1
-#endif
 #ifndef RT_STEP_UNROLL
 #define RT_STEP_UNROLL 2   // node steps between two looks at the leaf-phase condition (two votes + a branch per look): 1 / 2 / 3 / 4 =
                            // final scene 74.99 / 72.83 / 73.09 / 72.58 ms, mesh 114.5 / 111.3 / 116.1 / 121.1 (profiles/r02_traversal_ab.md)
@@ -243,11 +240,7 @@ __device__ __forceinline__ void closest_surface(const SceneView& sv, const Ray& 
         const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
         // two votes, not one __reduce_or_sync of a 2-bit state: VOTE.ANY writes a predicate the branch consumes directly,
         // REDUX goes through a uniform register (+2 % on the final scene and the 1M-triangle mesh, same-box A/B)
-#if RT_PHASE_MIN_BLOCKED > 1
-        const bool any_blocked = __popc(__ballot_sync(0xffffffffu, blocked)) >= RT_PHASE_MIN_BLOCKED, any_walking = __any_sync(0xffffffffu, node >= 0);
-#else
         const bool any_blocked = __any_sync(0xffffffffu, blocked), any_walking = __any_sync(0xffffffffu, node >= 0);
-#endif
         if (any_blocked || !any_walking) {
             if (parked != RT_NODE_DONE) {
                 const int prim = ~parked;
@@ -391,11 +384,7 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
             if (node < 0 && node != RT_NODE_DONE && parked == RT_NODE_DONE) { parked = node; node = pop(); }
         }
         const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
-#if RT_PHASE_MIN_BLOCKED > 1
-        const bool any_blocked = __popc(__ballot_sync(0xffffffffu, blocked)) >= RT_PHASE_MIN_BLOCKED, any_walking = __any_sync(0xffffffffu, node >= 0);
-#else
         const bool any_blocked = __any_sync(0xffffffffu, blocked), any_walking = __any_sync(0xffffffffu, node >= 0);
-#endif
         if (COUNT) (*steps) += RT_STEP_UNROLL;
         if (any_blocked || !any_walking) {
             if (parked != RT_NODE_DONE) {
