@@ -156,6 +156,9 @@ __device__ __forceinline__ WideHits wide_step(const WNode* np, const SlabRay& s,
 #ifndef RT_STACK_SENTINEL
 #define RT_STACK_SENTINEL 1   // final scene +1.4 %, big_scene1 +1.9 % (profiles/r02_traversal_ab.md)
 #endif
+#ifndef RT_STEP_UNROLL_DEFER
+#define RT_STEP_UNROLL_DEFER 2   // the same for walk_suspendable (1 M-triangle mesh: 1 / 2 / 3 / 4 = 114.5 / 111.3 / 116.1 / 121.1 ms)
+#endif
 #ifndef RT_STEP_UNROLL
 #define RT_STEP_UNROLL 2   // node steps between two looks at the leaf-phase condition (two votes + a branch per look): 1 / 2 / 3 / 4 =
                            // final scene 74.99 / 72.83 / 73.09 / 72.58 ms, mesh 114.5 / 111.3 / 116.1 / 121.1 (profiles/r02_traversal_ab.md)
@@ -359,7 +362,7 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
 #endif
     for (;;) {
         #pragma unroll
-        for (int unrolled = 0; unrolled < RT_STEP_UNROLL; unrolled++)
+        for (int unrolled = 0; unrolled < RT_STEP_UNROLL_DEFER; unrolled++)
         if (node >= 0) {
             if constexpr (WIDE) {
                 const WideHits h = wide_step(sv.wide + node, s, t_min, best.t);
@@ -385,7 +388,7 @@ __device__ __forceinline__ void walk_suspendable(const SceneView& sv, const Ray&
         }
         const bool blocked = node < 0 && node != RT_NODE_DONE;   // a second leaf while one is parked
         const bool any_blocked = __any_sync(0xffffffffu, blocked), any_walking = __any_sync(0xffffffffu, node >= 0);
-        if (COUNT) (*steps) += RT_STEP_UNROLL;
+        if (COUNT) (*steps) += RT_STEP_UNROLL_DEFER;
         if (any_blocked || !any_walking) {
             if (parked != RT_NODE_DONE) {
                 const int prim = ~parked;
